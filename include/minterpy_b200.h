@@ -1,0 +1,135 @@
+/*
+ * minterpy_b200.h -- C ABI of libminterpy_b200.so (hand-written CUDA for sm_100a).
+ *
+ * The reference (casus/minterpy) is pure Python + Numba and has no FFI of its own; the
+ * drop-in boundary is therefore the set of Python callables named in SURVEY.md section 8(b),
+ * and this header is what a ctypes binding for those callables needs.  Every entry point
+ * cites the reference function it replaces (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - plain C, no exceptions; every function returns an int status, 0 = MPX_OK.  The text
+ *     of the last error of the calling thread is returned by mpx_last_error().
+ *   - pointers without suffix are DEVICE pointers on the plan's device; `_h` = host memory.
+ *   - all matrices row-major with an explicit leading dimension (in elements).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Device
+ *     entry points only enqueue work; the `_host` variants synchronise before returning.
+ *   - there is no CPU fallback: without a CUDA device every call fails with MPX_ERR_CUDA.
+ */
+#ifndef MINTERPY_B200_H
+#define MINTERPY_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    MPX_OK = 0,
+    MPX_ERR_ARG = 1,        /* bad size / null pointer (reference: ValueError)              */
+    MPX_ERR_INCOMPLETE = 2, /* dds on a set that is not complete (core/tree.py:49-54)       */
+    MPX_ERR_CUDA = 3,       /* CUDA runtime error, message in mpx_last_error()              */
+    MPX_ERR_UNSUPPORTED = 4,/* shape outside the compiled kernel variants   */
+    MPX_ERR_NOMEM = 5
+};
+
+typedef struct mpx_plan mpx_plan;
+
+/* Library version, major*10000 + minor*100 + patch. */
+int mpx_version(void);
+
+/* Message of the calling thread's last failed call ("" if none). */
+const char *mpx_last_error(void);
+
+/*
+ * Build the immutable, device-resident description of one polynomial space: the
+ * exponent matrix of a MultiIndexSet and the generating points of its Grid.
+ *   replaces: the per-call preparation in eval_newton_monomials
+ *             (src/minterpy/utils.py:218-231: max_exponents, placeholders) and the
+ *             MultiIndexTree metadata used by dds (src/minterpy/core/tree.py:47-104,
+ *             src/minterpy/dds.py:30-235, 473-602).
+ * exponents_h: (N x m) int64 row-major, any row order, rows need not be unique or complete
+ *              for evaluation; mpx_dds additionally needs a lexicographically sorted,
+ *              complete (downward-closed) set and reports MPX_ERR_INCOMPLETE otherwise.
+ * gp_h:        (gp_rows x m) float64 row-major generating points; column i is read at rows
+ *              0 .. max_exponent_i (evaluation reads rows < max_exponent_i only, exactly as
+ *              src/minterpy/jit_compiled_utils.py:102-112).
+ */
+int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N, int m,
+                    const double *gp_h, int64_t gp_rows, mpx_plan **plan_out);
+void mpx_plan_destroy(mpx_plan *plan);
+
+/* Plan properties (host side, no device work). */
+enum {
+    MPX_INFO_N = 0,            /* number of monomials                                        */
+    MPX_INFO_M = 1,            /* spatial dimension                                          */
+    MPX_INFO_COMPLETE = 2,     /* 1 if sorted + downward closed (dds allowed)                */
+    MPX_INFO_EVAL_FMA = 3,     /* FP64 FMAs the evaluation kernel executes per point and
+                                  polynomial (tree form), for roofline accounting            */
+    MPX_INFO_DDS_UPDATES = 4,  /* elementary divided-difference updates per value column     */
+    MPX_INFO_LEAVES = 5,       /* number of dimension-0 fibers (tree leaves)                 */
+    MPX_INFO_DEVICE = 6,
+    MPX_INFO_SCRATCH_BYTES = 7,/* device scratch currently held by the plan                  */
+    MPX_INFO_EVAL_OTHER_FP64 = 8, /* FP64 adds/multiplies besides the FMAs, per point        */
+    MPX_INFO_CHUNKS = 9        /* chunks of the evaluation program                           */
+};
+int mpx_plan_info(const mpx_plan *plan, int what, int64_t *value_out);
+
+/*
+ * Evaluate k polynomials in Newton form at P points.
+ *   replaces: eval_newton_polynomials(xx, coefficients, exponents, generating_points)
+ *             src/minterpy/utils.py:247-343 (and its batch variant :346-399; the P x N
+ *             monomial matrix is never materialised, so batch_size has no meaning here).
+ * xx (P x m, ld_xx), coeffs (N x k, ld_c; row j belongs to exponent row j given to
+ * mpx_plan_create), out (P x k, ld_out).  P == 0 is a no-op.
+ * Uses plan-owned scratch (packed coefficients) that grows on demand: calls on one plan
+ * must be issued on one stream at a time.
+ */
+int mpx_eval(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+             const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
+             void *stream);
+
+/* Same, host buffers in and out (pinned or pageable): H2D, kernels and D2H are pipelined
+ * over blocks of points.  This is what the NumPy path of the Python mirror calls. */
+int mpx_eval_host(mpx_plan *plan, const double *xx_h, int64_t P, int64_t ld_xx,
+                  const double *coeffs_h, int k, int64_t ld_c, double *out_h,
+                  int64_t ld_out);
+
+/*
+ * The (P x N) matrix of Newton monomials.
+ *   replaces: eval_newton_monomials(x, exponents, generating_points, triangular)
+ *             src/minterpy/utils.py:177-244 -> src/minterpy/jit_compiled_utils.py:130-211.
+ * triangular != 0 reproduces the reference's lower-triangular mode (:187-199): row p gets
+ * monomials 0..p, the rest 0.0.  Results are bit-identical to the reference (same
+ * multiplication order, no FMA).
+ */
+int mpx_monomials(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx, double *out,
+                  int64_t ld_out, int triangular, void *stream);
+
+/*
+ * Multivariate divided differences, in place, on k value columns.
+ *   replaces: dds(fct_values, tree)  src/minterpy/dds.py:794-826 (jit_dds :697-791,
+ *             project_n_update :642-694, dds_1_dimensional :605-639).
+ * vals (N x k, ld): Lagrange coefficients (function values on the unisolvent nodes) in,
+ * Newton coefficients out.  The reference works on a copy; the Python mirror makes that
+ * copy.  Bit-identical to the reference (true IEEE division, same operation order).
+ */
+int mpx_dds(mpx_plan *plan, double *vals, int k, int64_t ld, void *stream);
+
+/* Same, host buffers: out_h (N x k) receives the result, in_h is not modified. */
+int mpx_dds_host(mpx_plan *plan, const double *in_h, int k, int64_t ld_in, double *out_h,
+                 int64_t ld_out);
+
+/*
+ * Dense operator apply out = T @ c.
+ *   replaces: MatrixOperator.__matmul__  src/minterpy/schemes/matrix_operator.py:13-22
+ * T (rows x cols, ld_t), c (cols x k, ld_c), out (rows x k, ld_out), all device, float64.
+ */
+int mpx_apply_dense(int device, const double *T, int64_t rows, int64_t cols, int64_t ld_t,
+                    const double *c, int k, int64_t ld_c, double *out, int64_t ld_out,
+                    void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MINTERPY_B200_H */

@@ -1,0 +1,99 @@
+// Internal declarations shared by the translation units of libminterpy_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/minterpy_b200.h"
+
+// ---- layout of the evaluation "program" (see DESIGN.md, section "Evaluation kernel") ----
+// The index set is compiled once per plan into chunks.  One chunk = a fixed-size block of
+// leaf records (descriptor words) plus the coefficient slots those leaves consume, so a CTA
+// can stream chunk after chunk through shared memory with two bulk copies per chunk.
+constexpr int MPX_DESC_WORDS = 512;   // u32 per chunk: [0]=number of words used, [4..] records
+constexpr int MPX_DESC_HDR = 4;
+constexpr int MPX_COEF_CAP = 1024;    // coefficient slots (doubles) per chunk and polynomial
+constexpr int MPX_STAGES = 3;         // shared-memory ring depth of the chunk stream
+constexpr int MPX_MAX_L0 = 66;        // dimension-0 table entries a thread can hold in registers
+constexpr int MPX_MAX_M = 16;
+
+// leaf record, one 32-bit word (plus extension words when MPX_D_IRREG is set):
+//   bits 0..5   number of coefficient PAIRS of the leaf (padded length / 2, 1..33)
+//   bits 6..13  exponent of the leaf in dimension 1 (table row of T1)
+//   bits 14..17 nf: how many upper levels (dimensions 2..) receive a fold after this leaf
+//   bit  18     irregular: advance/restart amounts follow in extension words
+//   bits 19..26 exponent of the advancing level before it advances (regular case)
+//   bit  27     last leaf of the program (no advance after the folds)
+constexpr uint32_t MPX_D_IRREG = 1u << 18;
+constexpr uint32_t MPX_D_LAST = 1u << 27;
+
+struct EvalProgram {
+    int n_chunks = 0;
+    int64_t n_leaves = 0;
+    int64_t fma_per_point = 0;     // leaf FMAs (padded) + level-1 FMAs + folds
+    int64_t other_fp64_per_point = 0;  // DADD/DMUL of running products and the tables
+    std::vector<uint32_t> desc;    // n_chunks * MPX_DESC_WORDS
+    std::vector<int32_t> slot_src; // n_chunks * MPX_COEF_CAP, row of the coefficient or -1
+};
+
+struct DdsDim {
+    int n_fibers = 0;
+    int max_len = 0;
+    int32_t *d_off = nullptr;   // n_fibers + 1
+    int32_t *d_rows = nullptr;  // N, rows grouped by fiber, in order of increasing exponent
+    double *d_diff = nullptr;   // (L x L) table: diff[l*L + r] = gp[r,d] - gp[l,d], L = max_len
+};
+
+struct mpx_plan {
+    int device = 0;
+    int64_t N = 0;
+    int m = 0;
+    int gp_rows = 0;                 // rows kept (max exponent over all dims + 1)
+    int max_exp[MPX_MAX_M] = {0};
+    int start_exp[MPX_MAX_M] = {0};  // exponents of the first leaf in dimensions >= 2
+    bool complete = false;
+    // evaluation
+    EvalProgram prog;
+    uint32_t *d_desc = nullptr;
+    int32_t *d_slot_src = nullptr;
+    double *d_gp = nullptr;          // (m x gp_rows) dimension-major copy of the generating points
+    uint8_t *d_exp8 = nullptr;       // (N x m) exponents as bytes, for the monomial kernel
+    int *d_max_exp = nullptr;        // (m) largest exponent per dimension
+    // dds
+    std::vector<DdsDim> dds;         // one per dimension (only if complete)
+    int64_t dds_updates = 0;
+    // growable scratch (packed coefficients of the current evaluation call)
+    std::mutex mu;
+    double *d_scratch = nullptr;
+    size_t scratch_bytes = 0;
+};
+
+// error plumbing --------------------------------------------------------------------------
+int mpx_fail(int code, const std::string &msg);
+#define MPX_CUDA(expr)                                                                     \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess)                                                             \
+            return mpx_fail(MPX_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) == cudaSuccess && cudaSetDevice(dev) == cudaSuccess) ok = true;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// kernels' host launchers (defined in the .cu files) ---------------------------------------
+int mpx_launch_eval(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+                    const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
+                    cudaStream_t stream);
+int mpx_launch_monomials(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+                         double *out, int64_t ld_out, int triangular, cudaStream_t stream);
+int mpx_launch_dds(mpx_plan *plan, double *vals, int k, int64_t ld, cudaStream_t stream);
+int mpx_ensure_scratch(mpx_plan *plan, size_t bytes);

@@ -1,0 +1,364 @@
+// Plan construction: compiles the exponent matrix into (a) the chunked leaf program the
+// evaluation kernel streams, (b) per-dimension fiber tables for the divided-difference
+// kernel, and uploads them together with the generating points.  Host-side integer work;
+// replaces the per-call preparation of src/minterpy/utils.py:218-231 and the tree metadata
+// of src/minterpy/core/tree.py:47-104 / src/minterpy/dds.py:30-235,473-602.
+#include <algorithm>
+#include <cstring>
+#include <memory>
+#include <numeric>
+
+#include "mpx_common.h"
+
+static thread_local std::string g_last_error;
+
+int mpx_fail(int code, const std::string &msg)
+{
+    g_last_error = msg;
+    return code;
+}
+
+extern "C" const char *mpx_last_error(void) { return g_last_error.c_str(); }
+extern "C" int mpx_version(void) { return 100; }
+
+namespace {
+
+// lexicographic order with the LAST column most significant (np.lexsort(exponents.T),
+// src/minterpy/core/utils.py:44-92)
+struct LexLess {
+    const int64_t *e;
+    int m;
+    bool operator()(int64_t a, int64_t b) const
+    {
+        for (int i = m - 1; i >= 0; --i) {
+            int64_t x = e[a * m + i], y = e[b * m + i];
+            if (x != y) return x < y;
+        }
+        return false;
+    }
+};
+
+int64_t find_sorted(const int64_t *e, const std::vector<int64_t> &order, int m,
+                    const int64_t *key)
+{
+    int64_t lo = 0, hi = (int64_t)order.size() - 1;
+    while (lo <= hi) {
+        int64_t mid = (lo + hi) >> 1;
+        const int64_t *row = e + order[mid] * m;
+        int c = 0;
+        for (int i = m - 1; i >= 0 && c == 0; --i) c = (row[i] < key[i]) ? -1 : (row[i] > key[i]);
+        if (c == 0) return mid;
+        if (c < 0) lo = mid + 1; else hi = mid - 1;
+    }
+    return -1;
+}
+
+// ---------------------------------------------------------------------------------------
+// Evaluation program.  Rows are visited in lexicographic order.  A LEAF is a maximal run
+// of rows with equal exponents in dimensions 1.. and strictly increasing dimension-0
+// exponent; its coefficients occupy slots 0..len-1 (len = largest e0 + 1, holes and the
+// even-length padding get slot_src = -1 => coefficient 0).
+// ---------------------------------------------------------------------------------------
+int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_t> &order,
+                    EvalProgram &pg, std::string &err)
+{
+    const int U = std::max(m - 2, 0);
+    struct Leaf { int64_t first, count; int len; };
+    std::vector<Leaf> leaves;
+    for (int64_t s = 0; s < N;) {
+        int64_t t = s + 1;
+        const int64_t *r0 = e + order[s] * m;
+        while (t < N) {
+            const int64_t *r1 = e + order[t] * m;
+            bool same = true;
+            for (int i = 1; i < m; ++i) same = same && (r1[i] == r0[i]);
+            if (!same || r1[0] <= e[order[t - 1] * m]) break;
+            ++t;
+        }
+        int len = (int)e[order[t - 1] * m] + 1;
+        leaves.push_back({s, t - s, len});
+        s = t;
+    }
+    pg.n_leaves = (int64_t)leaves.size();
+    pg.fma_per_point = 0;
+    pg.other_fp64_per_point = 0;
+
+    std::vector<uint32_t> words;   // words of the current chunk (records)
+    int coef_used = 0;
+    auto flush = [&]() {
+        size_t base = pg.desc.size();
+        pg.desc.resize(base + MPX_DESC_WORDS, 0u);
+        pg.desc[base] = (uint32_t)words.size();
+        std::copy(words.begin(), words.end(), pg.desc.begin() + base + MPX_DESC_HDR);
+        pg.n_chunks++;
+        pg.slot_src.resize((size_t)(pg.n_chunks + 1) * MPX_COEF_CAP, -1);   // room for the next chunk
+        words.clear();
+        coef_used = 0;
+    };
+    pg.desc.clear();
+    pg.slot_src.clear();
+    pg.n_chunks = 0;
+    pg.slot_src.resize(MPX_COEF_CAP, -1);
+
+    for (size_t li = 0; li < leaves.size(); ++li) {
+        const Leaf &lf = leaves[li];
+        const int64_t *cur = e + order[lf.first] * m;
+        const int64_t *nxt = (li + 1 < leaves.size()) ? e + order[leaves[li + 1].first] * m : nullptr;
+        const int lenp = (lf.len + 1) & ~1;
+        const int e1 = (m >= 2) ? (int)cur[1] : 0;
+        // highest dimension in which the next leaf differs
+        int D = 1;
+        bool last = (nxt == nullptr);
+        if (last) {
+            D = m - 1;
+        } else {
+            for (int i = m - 1; i >= 1; --i) if (nxt[i] != cur[i]) { D = i; break; }
+        }
+        int nf = last ? U : std::max(D - 1, 0);
+        std::vector<uint32_t> ext;
+        uint32_t w = (uint32_t)(lenp / 2) | ((uint32_t)e1 << 6) | ((uint32_t)nf << 14);
+        if (last) w |= MPX_D_LAST;
+        if (nf > 0 && !last) {
+            // level u = nf-1 (dimension D) advances from cur[D] to nxt[D]; levels below restart
+            int64_t adv = nxt[D] - cur[D];
+            bool regular = (adv == 1);
+            for (int i = 2; i < D; ++i) regular = regular && (nxt[i] == 0);
+            if (regular) {
+                w |= (uint32_t)cur[D] << 19;
+            } else {
+                w |= MPX_D_IRREG;
+                ext.push_back((uint32_t)cur[D] | ((uint32_t)adv << 8));
+                for (int i = 2; i < D; ++i) ext.push_back((uint32_t)nxt[i]);
+                pg.other_fp64_per_point += 2 * (adv - 1);
+                for (int i = 2; i < D; ++i) pg.other_fp64_per_point += 2 * nxt[i];
+            }
+            pg.other_fp64_per_point += 2;
+        }
+        int need_words = 1 + (int)ext.size();
+        if (coef_used + lenp > MPX_COEF_CAP ||
+            (int)words.size() + need_words > MPX_DESC_WORDS - MPX_DESC_HDR)
+            flush();
+        // coefficient slots of this leaf
+        int32_t *slots = pg.slot_src.data() + (size_t)pg.n_chunks * MPX_COEF_CAP + coef_used;
+        for (int64_t r = 0; r < lf.count; ++r) {
+            int64_t row = order[lf.first + r];
+            slots[e[row * m]] = (int32_t)row;
+        }
+        coef_used += lenp;
+        words.push_back(w);
+        for (uint32_t x : ext) words.push_back(x);
+        pg.fma_per_point += lenp + 1 + nf;
+    }
+    flush();
+    pg.slot_src.resize((size_t)pg.n_chunks * MPX_COEF_CAP);
+    (void)err;
+    return MPX_OK;
+}
+
+template <class T>
+int upload(T **dst, const std::vector<T> &src)
+{
+    if (src.empty()) { *dst = nullptr; return MPX_OK; }
+    MPX_CUDA(cudaMalloc((void **)dst, src.size() * sizeof(T)));
+    MPX_CUDA(cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return MPX_OK;
+}
+
+}  // namespace
+
+extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N, int m,
+                               const double *gp_h, int64_t gp_rows, mpx_plan **plan_out)
+{
+    if (!plan_out) return mpx_fail(MPX_ERR_ARG, "plan_out is null");
+    *plan_out = nullptr;
+    if (!exponents_h || !gp_h) return mpx_fail(MPX_ERR_ARG, "null input");
+    if (N < 1) return mpx_fail(MPX_ERR_ARG, "at least 1 monomial must be given");
+    if (m < 1) return mpx_fail(MPX_ERR_ARG, "spatial dimension must be >= 1");
+    if (m > MPX_MAX_M)
+        return mpx_fail(MPX_ERR_UNSUPPORTED, "spatial dimension > 16 is not supported");
+    if (N > INT32_MAX / 2) return mpx_fail(MPX_ERR_UNSUPPORTED, "too many monomials");
+
+    mpx_plan *pl = new mpx_plan();
+    std::unique_ptr<mpx_plan, void (*)(mpx_plan *)> guard(pl, mpx_plan_destroy);
+    pl->device = device;
+    pl->N = N;
+    pl->m = m;
+    const int64_t *e = exponents_h;
+    for (int64_t j = 0; j < N; ++j)
+        for (int i = 0; i < m; ++i) {
+            int64_t v = e[j * m + i];
+            if (v < 0) return mpx_fail(MPX_ERR_ARG, "negative exponent");
+            if (v > 255) return mpx_fail(MPX_ERR_UNSUPPORTED, "exponent > 255 is not supported");
+            if (v > pl->max_exp[i]) pl->max_exp[i] = (int)v;
+        }
+    int maxmax = 0;
+    for (int i = 0; i < m; ++i) {
+        // evaluation reads rows < max_exp[i] (jit_compiled_utils.py:102-112)
+        if (pl->max_exp[i] > gp_rows)
+            return mpx_fail(MPX_ERR_ARG, "generating_points has fewer rows than the largest exponent");
+        maxmax = std::max(maxmax, pl->max_exp[i]);
+    }
+    if (pl->max_exp[0] + 1 > MPX_MAX_L0 - 1)
+        return mpx_fail(MPX_ERR_UNSUPPORTED,
+                        "exponent in dimension 0 exceeds 64 (register table of the evaluation kernel)");
+    pl->gp_rows = (int)std::min<int64_t>(gp_rows, maxmax + 1);
+
+    // lexicographic order (identity for a MultiIndexSet, which is always sorted)
+    std::vector<int64_t> order(N);
+    std::iota(order.begin(), order.end(), 0);
+    LexLess less{e, m};
+    bool sorted_unique = true;
+    for (int64_t j = 1; j < N && sorted_unique; ++j) sorted_unique = less(j - 1, j);
+    if (!sorted_unique) std::stable_sort(order.begin(), order.end(), less);
+
+    // completeness (downward closed): every row with e_d > 0 has its predecessor along d
+    bool complete = sorted_unique;
+    for (int i = 0; i < m && complete; ++i)
+        if (pl->max_exp[i] >= gp_rows) complete = false;    // dds reads row max_exp too
+    std::vector<int64_t> key(m);
+    for (int64_t j = 0; j < N && complete; ++j)
+        for (int i = 0; i < m && complete; ++i)
+            if (e[j * m + i] > 0) {
+                std::copy(e + j * m, e + j * m + m, key.begin());
+                key[i] -= 1;
+                if (find_sorted(e, order, m, key.data()) < 0) complete = false;
+            }
+    pl->complete = complete;
+
+    std::string err;
+    int rc = compile_program(e, N, m, order, pl->prog, err);
+    if (rc != MPX_OK) return mpx_fail(rc, err);
+    // upper-level exponents of the first leaf (0 for every downward-closed set)
+    for (int i = 2; i < m; ++i) {
+        pl->start_exp[i] = (int)e[order[0] * m + i];
+        pl->prog.other_fp64_per_point += 2 * pl->start_exp[i];
+    }
+    // table building cost per point: one DADD + one DMUL per table entry
+    for (int i = 0; i < m; ++i) pl->prog.other_fp64_per_point += 2 * pl->max_exp[i];
+
+    DeviceGuard dg(device);
+    if (!dg.ok) return mpx_fail(MPX_ERR_CUDA, "cannot select CUDA device (no GPU or bad index)");
+
+    if ((rc = upload(&pl->d_desc, pl->prog.desc)) != MPX_OK) return rc;
+    if ((rc = upload(&pl->d_slot_src, pl->prog.slot_src)) != MPX_OK) return rc;
+    std::vector<double> gpt((size_t)m * pl->gp_rows);
+    for (int i = 0; i < m; ++i)
+        for (int j = 0; j < pl->gp_rows; ++j) gpt[(size_t)i * pl->gp_rows + j] = gp_h[(size_t)j * m + i];
+    if ((rc = upload(&pl->d_gp, gpt)) != MPX_OK) return rc;
+    std::vector<uint8_t> e8((size_t)N * m);
+    for (size_t t = 0; t < e8.size(); ++t) e8[t] = (uint8_t)e[t];
+    if ((rc = upload(&pl->d_exp8, e8)) != MPX_OK) return rc;
+    std::vector<int> mxv(pl->max_exp, pl->max_exp + m);
+    if ((rc = upload(&pl->d_max_exp, mxv)) != MPX_OK) return rc;
+
+    // fiber tables for the divided differences
+    if (complete) {
+        pl->dds.resize(m);
+        std::vector<int64_t> succ(N);
+        for (int d = 0; d < m; ++d) {
+            for (int64_t j = 0; j < N; ++j) {
+                std::copy(e + j * m, e + j * m + m, key.begin());
+                key[d] += 1;
+                succ[j] = (key[d] <= pl->max_exp[d]) ? find_sorted(e, order, m, key.data()) : -1;
+            }
+            std::vector<int32_t> off, rows;
+            rows.reserve(N);
+            int max_len = 0;
+            for (int64_t j0 = 0; j0 < N; ++j0) {
+                if (e[j0 * m + d] != 0) continue;
+                off.push_back((int32_t)rows.size());
+                int len = 0;
+                for (int64_t j = j0; j >= 0; j = succ[j]) { rows.push_back((int32_t)j); ++len; }
+                max_len = std::max(max_len, len);
+                pl->dds_updates += (int64_t)len * (len - 1) / 2;
+            }
+            off.push_back((int32_t)rows.size());
+            DdsDim &dd = pl->dds[d];
+            dd.n_fibers = (int)off.size() - 1;
+            dd.max_len = max_len;
+            std::vector<double> diff((size_t)max_len * max_len, 1.0);
+            for (int l = 0; l < max_len; ++l)
+                for (int r = 0; r < max_len; ++r)
+                    if (r != l)   // gp[r,d] - gp[l,d], as src/minterpy/dds.py:673-679 / :633
+                        diff[(size_t)l * max_len + r] = gp_h[(size_t)r * m + d] - gp_h[(size_t)l * m + d];
+            if ((rc = upload(&dd.d_off, off)) != MPX_OK) return rc;
+            if ((rc = upload(&dd.d_rows, rows)) != MPX_OK) return rc;
+            if ((rc = upload(&dd.d_diff, diff)) != MPX_OK) return rc;
+        }
+    }
+    guard.release();
+    *plan_out = pl;
+    return MPX_OK;
+}
+
+extern "C" void mpx_plan_destroy(mpx_plan *pl)
+{
+    if (!pl) return;
+    DeviceGuard dg(pl->device);
+    cudaFree(pl->d_desc);
+    cudaFree(pl->d_slot_src);
+    cudaFree(pl->d_gp);
+    cudaFree(pl->d_exp8);
+    cudaFree(pl->d_max_exp);
+    cudaFree(pl->d_scratch);
+    for (DdsDim &dd : pl->dds) {
+        cudaFree(dd.d_off);
+        cudaFree(dd.d_rows);
+        cudaFree(dd.d_diff);
+    }
+    delete pl;
+}
+
+extern "C" int mpx_plan_info(const mpx_plan *pl, int what, int64_t *value_out)
+{
+    if (!pl || !value_out) return mpx_fail(MPX_ERR_ARG, "null argument");
+    switch (what) {
+    case MPX_INFO_N: *value_out = pl->N; break;
+    case MPX_INFO_M: *value_out = pl->m; break;
+    case MPX_INFO_COMPLETE: *value_out = pl->complete ? 1 : 0; break;
+    case MPX_INFO_EVAL_FMA: *value_out = pl->prog.fma_per_point; break;
+    case MPX_INFO_EVAL_OTHER_FP64: *value_out = pl->prog.other_fp64_per_point; break;
+    case MPX_INFO_DDS_UPDATES: *value_out = pl->dds_updates; break;
+    case MPX_INFO_LEAVES: *value_out = pl->prog.n_leaves; break;
+    case MPX_INFO_DEVICE: *value_out = pl->device; break;
+    case MPX_INFO_SCRATCH_BYTES: *value_out = (int64_t)pl->scratch_bytes; break;
+    case MPX_INFO_CHUNKS: *value_out = pl->prog.n_chunks; break;
+    default: return mpx_fail(MPX_ERR_ARG, "unknown info key");
+    }
+    return MPX_OK;
+}
+
+int mpx_ensure_scratch(mpx_plan *pl, size_t bytes)
+{
+    if (bytes <= pl->scratch_bytes) return MPX_OK;
+    if (pl->d_scratch) MPX_CUDA(cudaFree(pl->d_scratch));
+    pl->d_scratch = nullptr;
+    pl->scratch_bytes = 0;
+    size_t want = std::max(bytes, (size_t)1 << 20);
+    MPX_CUDA(cudaMalloc((void **)&pl->d_scratch, want));
+    pl->scratch_bytes = want;
+    return MPX_OK;
+}
+
+// Host-only view of the compiled evaluation program, for tests of the index-set compiler
+// (no device needed).  desc_out / slot_out may be null to query the sizes.
+extern "C" int mpx_debug_program(const int64_t *exponents_h, int64_t N, int m, uint32_t *desc_out,
+                                 int32_t *slot_out, int64_t *n_chunks_out, int64_t *fma_out)
+{
+    if (!exponents_h || N < 1 || m < 1 || m > MPX_MAX_M) return mpx_fail(MPX_ERR_ARG, "bad argument");
+    for (int64_t t = 0; t < N * m; ++t)
+        if (exponents_h[t] < 0 || exponents_h[t] > 255) return mpx_fail(MPX_ERR_UNSUPPORTED, "exponent out of range");
+    std::vector<int64_t> order(N);
+    std::iota(order.begin(), order.end(), 0);
+    LexLess less{exponents_h, m};
+    std::stable_sort(order.begin(), order.end(), less);
+    EvalProgram pg;
+    std::string err;
+    int rc = compile_program(exponents_h, N, m, order, pg, err);
+    if (rc != MPX_OK) return mpx_fail(rc, err);
+    if (n_chunks_out) *n_chunks_out = pg.n_chunks;
+    if (fma_out) *fma_out = pg.fma_per_point;
+    if (desc_out) std::copy(pg.desc.begin(), pg.desc.end(), desc_out);
+    if (slot_out) std::copy(pg.slot_src.begin(), pg.slot_src.end(), slot_out);
+    return MPX_OK;
+}

@@ -1,0 +1,62 @@
+"""Route an installed minterpy's hot path through the CUDA library.
+
+``install()`` rebinds the names the reference binds at import time
+(``polynomials/newton_polynomial.py:10-11``, ``interpolation.py:15``,
+``transformations/utils.py:10,18``) and the operator builders of ``LagrangeToNewton`` /
+``NewtonToLagrange`` (``transformations/lagrange.py:23``, ``transformations/newton.py:32``).
+``uninstall()`` restores the originals.
+"""
+import importlib
+
+from . import api
+from .polynomials import DDSOperator, NodeEvalOperator
+
+_saved = []
+
+
+def _set(obj, name, value):
+    _saved.append((obj, name, obj.__dict__.get(name, getattr(obj, name))))
+    setattr(obj, name, value)
+
+
+def install():
+    if _saved:
+        return
+    mods = {n: importlib.import_module(n) for n in (
+        "minterpy.utils", "minterpy.dds", "minterpy.interpolation",
+        "minterpy.polynomials.newton_polynomial", "minterpy.transformations.utils",
+        "minterpy.transformations.lagrange", "minterpy.transformations.newton")}
+    _set(mods["minterpy.utils"], "eval_newton_polynomials", api.eval_newton_polynomials)
+    _set(mods["minterpy.utils"], "eval_newton_monomials", api.eval_newton_monomials)
+    _set(mods["minterpy.polynomials.newton_polynomial"], "eval_newton_polynomials",
+         api.eval_newton_polynomials)
+    for name in ("minterpy.dds", "minterpy.interpolation",
+                 "minterpy.polynomials.newton_polynomial", "minterpy.transformations.utils"):
+        _set(mods[name], "dds", api.dds)
+    _set(mods["minterpy.transformations.utils"], "eval_newton_monomials",
+         api.eval_newton_monomials)
+
+    def l2n_operator(transformation):
+        grid = transformation.grid
+        if grid.multi_index.is_complete and not transformation.origin_poly.indices_are_separate:
+            return DDSOperator(grid)
+        return _orig_l2n(transformation)
+
+    def n2l_operator(transformation):
+        grid = transformation.grid
+        if not transformation.origin_poly.indices_are_separate:
+            return NodeEvalOperator(grid)
+        return _orig_n2l(transformation)
+
+    l2n_cls = mods["minterpy.transformations.lagrange"].LagrangeToNewton
+    n2l_cls = mods["minterpy.transformations.newton"].NewtonToLagrange
+    _orig_l2n = l2n_cls.__dict__["_get_transformation_operator"]
+    _orig_n2l = n2l_cls.__dict__["_get_transformation_operator"]
+    _set(l2n_cls, "_get_transformation_operator", l2n_operator)
+    _set(n2l_cls, "_get_transformation_operator", n2l_operator)
+
+
+def uninstall():
+    while _saved:
+        obj, name, value = _saved.pop()
+        setattr(obj, name, value)

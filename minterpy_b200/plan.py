@@ -1,0 +1,156 @@
+"""`Plan`: the device-resident description of one polynomial space (index set + grid).
+
+Wraps ``mpx_plan_*`` / ``mpx_eval*`` / ``mpx_dds*`` / ``mpx_monomials`` of the C ABI.  NumPy
+arrays go through the ``*_host`` entry points (the library does the transfers); CUDA torch
+tensors are passed by ``data_ptr()`` without a copy and results come back as torch tensors.
+"""
+import ctypes
+import threading
+
+import numpy as np
+
+from . import _lib
+
+_cache = {}
+_cache_lock = threading.Lock()
+_CACHE_MAX = 32
+
+
+def _is_torch(a):
+    return type(a).__module__.split(".")[0] == "torch"
+
+
+def _current_device():
+    import torch
+    if not torch.cuda.is_available():
+        raise _lib.MinterpyB200Error("no CUDA device available; minterpy_b200 has no CPU fallback")
+    return torch.cuda.current_device()
+
+
+class Plan:
+    def __init__(self, exponents, generating_points, device=None):
+        e = np.ascontiguousarray(exponents, dtype=np.int64)
+        gp = np.ascontiguousarray(generating_points, dtype=np.float64)
+        if e.ndim != 2 or gp.ndim != 2:
+            raise ValueError("exponents and generating_points must be 2-D")
+        if gp.shape[1] != e.shape[1]:
+            raise ValueError(
+                f"generating_points has {gp.shape[1]} columns but the exponents have {e.shape[1]}")
+        if device is None:
+            device = _current_device()
+        self.device = int(device)
+        self.N, self.m = e.shape
+        handle = ctypes.c_void_p()
+        rc = _lib.lib().mpx_plan_create(self.device, e.ctypes.data, self.N, self.m,
+                                        gp.ctypes.data, gp.shape[0], ctypes.byref(handle))
+        _lib.check(rc)
+        self._h = handle
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                _lib.lib().mpx_plan_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    def info(self, what):
+        v = ctypes.c_int64()
+        _lib.check(_lib.lib().mpx_plan_info(self._h, what, ctypes.byref(v)))
+        return v.value
+
+    @property
+    def is_complete(self):
+        return bool(self.info(_lib.INFO_COMPLETE))
+
+    # ---- evaluation ---------------------------------------------------------------------
+    def eval(self, xx, coeffs):
+        """xx (P, m), coeffs (N, k) -> (P, k).  NumPy in -> NumPy out, torch in -> torch out."""
+        if _is_torch(xx) or _is_torch(coeffs):
+            return self._eval_torch(xx, coeffs)
+        xx = np.ascontiguousarray(xx, dtype=np.float64)
+        coeffs = np.ascontiguousarray(coeffs, dtype=np.float64)
+        P, k = xx.shape[0], coeffs.shape[1]
+        out = np.empty((P, k), dtype=np.float64)
+        if P:
+            rc = _lib.lib().mpx_eval_host(self._h, xx.ctypes.data, P, self.m, coeffs.ctypes.data,
+                                          k, k, out.ctypes.data, k)
+            _lib.check(rc)
+        return out
+
+    def _eval_torch(self, xx, coeffs, out=None):
+        import torch
+        dev = torch.device("cuda", self.device)
+        xx = torch.as_tensor(xx, dtype=torch.float64, device=dev)
+        coeffs = torch.as_tensor(coeffs, dtype=torch.float64, device=dev)
+        if xx.stride(-1) != 1:
+            xx = xx.contiguous()
+        if coeffs.stride(-1) != 1:
+            coeffs = coeffs.contiguous()
+        P, k = xx.shape[0], coeffs.shape[1]
+        if out is None:
+            out = torch.empty((P, k), dtype=torch.float64, device=dev)
+        if P:
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            rc = _lib.lib().mpx_eval(self._h, xx.data_ptr(), P, xx.stride(0), coeffs.data_ptr(), k,
+                                     coeffs.stride(0), out.data_ptr(), out.stride(0), stream)
+            _lib.check(rc)
+        return out
+
+    def monomials(self, xx, triangular=False):
+        """(P, N) Newton monomial matrix."""
+        import torch
+        dev = torch.device("cuda", self.device)
+        as_numpy = not _is_torch(xx)
+        x = torch.as_tensor(np.ascontiguousarray(xx) if as_numpy else xx, dtype=torch.float64,
+                            device=dev).contiguous()
+        P = x.shape[0]
+        out = torch.empty((P, self.N), dtype=torch.float64, device=dev)
+        if P:
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            rc = _lib.lib().mpx_monomials(self._h, x.data_ptr(), P, x.stride(0), out.data_ptr(),
+                                          out.stride(0), int(bool(triangular)), stream)
+            _lib.check(rc)
+        return out.cpu().numpy() if as_numpy else out
+
+    # ---- divided differences ----------------------------------------------------------------
+    def dds(self, values):
+        """values (N, k) -> Newton coefficients (N, k); the input is never modified."""
+        if _is_torch(values):
+            import torch
+            dev = torch.device("cuda", self.device)
+            v = torch.as_tensor(values, dtype=torch.float64, device=dev).clone(
+                memory_format=torch.contiguous_format)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            rc = _lib.lib().mpx_dds(self._h, v.data_ptr(), v.shape[1], v.stride(0), stream)
+            _lib.check(rc)
+            return v
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        out = np.empty_like(values)
+        k = values.shape[1]
+        rc = _lib.lib().mpx_dds_host(self._h, values.ctypes.data, k, k, out.ctypes.data, k)
+        _lib.check(rc)
+        return out
+
+
+def get_plan(exponents, generating_points, device=None):
+    """Plan for (exponents, generating_points) on `device`, cached by content."""
+    e = np.ascontiguousarray(exponents, dtype=np.int64)
+    gp = np.ascontiguousarray(generating_points, dtype=np.float64)
+    if device is None:
+        device = _current_device()
+    key = (int(device), e.shape, gp.shape, hash(e.tobytes()), hash(gp.tobytes()))
+    with _cache_lock:
+        plan = _cache.get(key)
+        if plan is None:
+            plan = Plan(e, gp, device)
+            if len(_cache) >= _CACHE_MAX:
+                _cache.pop(next(iter(_cache)))
+            _cache[key] = plan
+    return plan
+
+
+def clear_plan_cache():
+    with _cache_lock:
+        _cache.clear()

@@ -1,0 +1,96 @@
+"""Pure-Python interpreter of the evaluation program the plan compiler emits
+(minterpy_b200/csrc/mpx_plan.cu: compile_program; record format in mpx_common.h).
+
+Test infrastructure: lets the CPU suite check the index-set compiler -- leaf records,
+fold counts, irregular extensions, coefficient slots -- without a GPU, by evaluating the
+program exactly the way the CUDA kernel walks it (mpx_eval.cu: eval_tree_kernel).
+"""
+import ctypes
+
+import numpy as np
+
+from minterpy_b200 import _lib
+
+DESC_WORDS, DESC_HDR, COEF_CAP = 512, 4, 1024
+D_IRREG, D_LAST = 1 << 18, 1 << 27
+
+
+def compile_program(exponents):
+    e = np.ascontiguousarray(exponents, dtype=np.int64)
+    N, m = e.shape
+    nch, fma = ctypes.c_int64(), ctypes.c_int64()
+    lib = _lib.lib()
+    _lib.check(lib.mpx_debug_program(e.ctypes.data, N, m, None, None, ctypes.byref(nch),
+                                     ctypes.byref(fma)))
+    desc = np.zeros(nch.value * DESC_WORDS, dtype=np.uint32)
+    slots = np.zeros(nch.value * COEF_CAP, dtype=np.int32)
+    _lib.check(lib.mpx_debug_program(e.ctypes.data, N, m, desc.ctypes.data, slots.ctypes.data,
+                                     ctypes.byref(nch), ctypes.byref(fma)))
+    return desc.reshape(-1, DESC_WORDS), slots.reshape(-1, COEF_CAP), fma.value
+
+
+def run_program(desc, slots, x, coeffs, exponents, gp):
+    """Value of sum_j coeffs[j] * N_j(x) for ONE point x, walking the program."""
+    e = np.asarray(exponents)
+    N, m = e.shape
+    U = max(m - 2, 0)
+    mx = e.max(axis=0)
+    order = np.lexsort(e.T)
+    T0 = np.zeros(66)
+    T0[0] = 1.0
+    for j in range(mx[0]):
+        T0[j + 1] = T0[j] * (x[0] - gp[j, 0])
+    T1 = np.ones(int(mx[1]) + 1 if m >= 2 else 1)
+    if m >= 2:
+        for j in range(mx[1]):
+            T1[j + 1] = T1[j] * (x[1] - gp[j, 1])
+    xu = [x[2 + u] for u in range(U)]
+    t = [1.0] * U
+    for u in range(U):
+        for j in range(int(e[order[0], 2 + u])):
+            t[u] *= xu[u] - gp[j, 2 + u]
+    acc = [0.0] * U
+    acc1 = 0.0
+    fma = 0
+    for c in range(desc.shape[0]):
+        dw = desc[c]
+        packed = np.where(slots[c] >= 0, coeffs[np.maximum(slots[c], 0)], 0.0)
+        cp = 0
+        i = DESC_HDR
+        end = DESC_HDR + int(dw[0])
+        while i < end:
+            w = int(dw[i])
+            np_, e1, nf = w & 63, (w >> 6) & 255, (w >> 14) & 15
+            a = 0.0
+            for s in range(2 * np_ - 1, -1, -1):
+                a += packed[cp + s] * T0[s]
+                fma += 1
+            cp += 2 * np_
+            acc1 += T1[e1] * a
+            fma += 1
+            if nf:
+                adv, cur = 1, (w >> 19) & 255
+                irregular, last = bool(w & D_IRREG), bool(w & D_LAST)
+                if irregular:
+                    i += 1
+                    cur, adv = int(dw[i]) & 255, int(dw[i]) >> 8
+                low, acc1 = acc1, 0.0
+                for u in range(nf):
+                    av = acc[u] + t[u] * low
+                    fma += 1
+                    if u < nf - 1:
+                        low, acc[u] = av, 0.0
+                        tn = 1.0
+                        if irregular:
+                            for j in range(int(dw[i + 1 + u])):
+                                tn *= xu[u] - gp[j, 2 + u]
+                        t[u] = tn
+                    else:
+                        acc[u] = av
+                        if not last:
+                            for j in range(adv):
+                                t[u] *= xu[u] - gp[cur + j, 2 + u]
+                if irregular:
+                    i += nf - 1
+            i += 1
+    return (acc[U - 1] if U > 0 else acc1), fma
