@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""Benchmark of the Newton-evaluation hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--impl reference]
+
+One "step" = one pass of the evaluation kernel over one batch of synthetic query points.
+At N = 1 the workload is BASELINE config 2 (m=4, n=16, lp=2, 1e8 points); with N > 1 (torchrun,
+one rank per GPU) every rank evaluates its own 1e8-point shard (weak scaling, no data-path
+collective; the coefficients are broadcast once over NCCL before the timed region).
+
+value  = point x monomial evaluations per second, inputs resident in HBM (CUDA events on the
+         launching stream, max over ranks);
+e2e    = the same metric through the public NumPy API with pinned HOST buffers (H2D of the
+         points and D2H of the values inside the timed region);
+roofline = executed FP64 flops of the evaluation kernel / its CUDA-event duration, against
+         the DFMA peak measured on this box by tools/fp64_peak.cu (MEASURED_PEAKS.json has no
+         FP64 figure) -- nominal 37.2 TFLOP/s is reported beside it;
+cpu_baseline = the CPU oracle (a C restatement of the reference's algorithm, all host
+         threads) on a bounded sample of the same workload.
+`--impl reference` times only that CPU path.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+
+import golden_io  # noqa: E402
+
+WORKLOADS = {
+    # tag: (description, points per GPU, k)
+    "cfg1": ("m=1 n=64 lp=2 (README quickstart), 1e6 points", 1_000_000, 1),
+    "cfg2": ("m=4 n=16 lp=2, 1e8 points in [-1,1]^4", 100_000_000, 1),
+    "cfg3": ("m=6 n=10 lp=1, k=64 polynomials, 1e7 points", 10_000_000, 64),
+    "cfg4": ("m=5 n=12 lp=2, k=256 polynomials, 1e6 points", 1_000_000, 256),
+    "cfg5": ("m=3 n=32 lp=inf, 1.25e8 points per GPU (1e9 over 8)", 125_000_000, 1),
+}
+NOMINAL_FP64_TFLOPS = 37.2   # 148 SM x 64 DFMA/clk x 2 x 1.965 GHz
+
+
+def load_workload(tag):
+    g = golden_io.load(tag)
+    return g["exponents"], g["generating_points"]
+
+
+def model_flops_per_point(e, k):
+    """F/P = N (1 + 2k) + 2 sum_i max_exp_i."""
+    return e.shape[0] * (1 + 2 * k) + 2 * int(e.max(axis=0).sum())
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        for ts, line in self.lines:
+            if ts < t0 or ts > t1 + 0.2:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax = float(f[2])
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                  "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_fp64_peak():
+    """Best DFMA rate of tools/fp64_peak.cu on this GPU (TFLOP/s), or None."""
+    exe = os.path.join(ROOT, "tools", "_bin", "fp64_peak")
+    if not os.path.exists(exe):
+        return None, None
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120).stdout
+    except (OSError, subprocess.TimeoutExpired):
+        return None, None
+    dfma, dmma = [], []
+    for line in out.splitlines():
+        try:
+            d = json.loads(line)
+        except ValueError:
+            continue
+        if d.get("bench", "").startswith("dfma_ch"):
+            dfma.append(d["tflops"])
+        if d.get("bench", "").startswith("dmma"):
+            dmma.append(d["tflops"])
+    return (max(dfma) if dfma else None), (max(dmma) if dmma else None)
+
+
+def cpu_baseline(e, gp, k, target_seconds=12.0, seed=1):
+    """Oracle port on all host threads over a bounded sample of the workload."""
+    import oracle
+    cores = oracle.num_threads()
+    N, m = e.shape
+    rng = np.random.default_rng(seed)
+    c = rng.uniform(-1, 1, (N, k))
+    probe = max(cores * 8, 64)
+    xx = rng.uniform(-1, 1, (probe, m))
+    t = time.perf_counter()
+    oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=cores)
+    rate = probe / max(time.perf_counter() - t, 1e-6)
+    P = int(max(probe, min(rate * target_seconds, 5_000_000)))
+    xx = rng.uniform(-1, 1, (P, m))
+    t = time.perf_counter()
+    oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=cores)
+    dt = time.perf_counter() - t
+    return {"value": P * N / dt, "unit": "point*monomials/s", "cores": cores, "kind": "port",
+            "sample": f"{P} points of the workload ({dt:.1f} s), oracle/newton_oracle.c on "
+                      f"{cores} threads", "seconds": dt, "points": P}
+
+
+def run_reference(args):
+    """`--impl reference`: the CPU path only (rank 0; other ranks exit)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    e, gp = load_workload(args.workload)
+    desc, _, k = WORKLOADS[args.workload]
+    N = e.shape[0]
+    per_step = max(4.0, min(30.0, 150.0 / max(args.steps + args.warmup, 1)))
+    for _ in range(args.warmup):
+        cpu_baseline(e, gp, k, target_seconds=1.0)
+    vals, pts, secs = [], 0, 0.0
+    for s in range(args.steps):
+        b = cpu_baseline(e, gp, k, target_seconds=per_step, seed=100 + s)
+        vals.append(b["value"])
+        pts += b["points"]
+        secs += b["seconds"]
+    value = pts * N / secs
+    import oracle
+    line = {"impl": "reference", "metric": "newton_evals_per_sec", "value": value,
+            "unit": "point*monomials/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(args.steps, 1),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": {"workload": f"{args.workload}: {desc}",
+                                            "monomials": int(N), "k": k},
+            "cpu_baseline": {"value": value, "unit": "point*monomials/s",
+                             "cores": oracle.num_threads(), "kind": "port",
+                             "sample": f"{pts} points over {args.steps} steps"},
+            "e2e": {"value": value, "unit": "point*monomials/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--points", type=int, default=None, help="points per GPU (default: workload's)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import minterpy_b200 as mpb
+    from minterpy_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    desc, P, k = WORKLOADS[args.workload]
+    if args.points:
+        P = args.points
+    cfg = int(args.workload[3:])
+    e, gp = load_workload(args.workload)
+    N, m = e.shape
+    plan = mpb.get_plan(e, gp, device=local)
+
+    # synthetic inputs: points per rank from Philox on the device; coefficients drawn on rank 0
+    # and broadcast once over NCCL (the only collective; it is outside the timed region)
+    gen = torch.Generator(device=dev).manual_seed(20261106 + 1000 * cfg + rank)
+    xx = torch.rand((P, m), generator=gen, dtype=torch.float64, device=dev) * 2 - 1
+    coeffs = torch.from_numpy(golden_io.draw_uniform(7 + cfg, (N, k))).to(dev)
+    if world > 1:
+        if rank != 0:
+            coeffs.zero_()
+        dist.broadcast(coeffs, src=0)
+    out = torch.empty((P, k), dtype=torch.float64, device=dev)
+
+    def step():
+        plan._eval_torch(xx, coeffs, out=out)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    barrier()
+    t0 = time.time()
+    evs[0].record()
+    for i in range(args.steps):
+        step()
+        evs[i + 1].record()
+    barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+    step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    total_ms = evs[0].elapsed_time(evs[-1])
+    if world > 1:
+        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = t.item()
+    ms_per_step = total_ms / args.steps
+    value = world * P * N / (ms_per_step * 1e-3)
+
+    # ---- end to end through the public NumPy API, pinned host buffers --------------------
+    e2e = None
+    if not args.no_e2e:
+        Pe = P
+        xh = torch.empty((Pe, m), dtype=torch.float64, pin_memory=True)
+        xh.copy_(xx[:Pe])
+        xh_np = xh.numpy()
+        ch = coeffs.cpu().numpy()
+        ch1 = ch[:, 0] if k == 1 else ch
+        e2e_steps = max(1, min(args.steps, 3))
+        mpb.eval_newton_polynomials(xh_np, ch1, e, gp)          # warm-up
+        barrier()
+        t = time.perf_counter()
+        for _ in range(e2e_steps):
+            y = mpb.eval_newton_polynomials(xh_np, ch1, e, gp)
+        barrier()
+        dt = (time.perf_counter() - t) / e2e_steps
+        if world > 1:
+            tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = tt.item()
+        assert y.shape[0] == Pe
+        e2e = {"value": world * Pe * N / dt, "unit": "point*monomials/s",
+               "h2d_bytes_per_step": int(Pe * m * 8 + N * k * 8), "d2h_bytes_per_step": int(Pe * k * 8),
+               "ms_per_step": dt * 1e3, "api": "minterpy_b200.eval_newton_polynomials(numpy)"}
+        del xh
+
+    gather_ms = None
+    if world > 1:
+        full = torch.empty((world * P, k), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(full, out)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        dist.all_gather_into_tensor(full, out)
+        g1.record()
+        barrier()
+        gather_ms = g0.elapsed_time(g1)
+        del full
+
+    if rank == 0:
+        fma = plan.info(_lib.INFO_EVAL_FMA)
+        other = plan.info(_lib.INFO_EVAL_OTHER_FP64)
+        executed = (2 * fma + other) * k          # FP64 flops per point actually issued
+        model = model_flops_per_point(e, k)
+        algo = min(model, executed)
+        peak_dfma, peak_dmma = measured_fp64_peak()
+        peak = peak_dfma or NOMINAL_FP64_TFLOPS
+        kernel_ms = float(np.median(step_ms))
+        achieved = algo * P / (kernel_ms * 1e-3) / 1e12
+        roofline = {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                    "frac": achieved / peak, "traffic": None,
+                    "peak_source": ("measured DFMA rate, tools/fp64_peak.cu on this GPU"
+                                    if peak_dfma else "nominal (fp64_peak tool missing)"),
+                    "nominal_peak": NOMINAL_FP64_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP64_TFLOPS,
+                    "measured_dmma_peak": peak_dmma,
+                    "flops_per_point_model": model, "flops_per_point_executed": executed,
+                    "fma_per_point": fma * k, "kernel": "eval_tree_kernel",
+                    "kernel_ms": kernel_ms,
+                    "hbm_gbs": P * 8 * (m + k) / (kernel_ms * 1e-3) / 1e9}
+        cpu = None if args.no_cpu else cpu_baseline(e, gp, k)
+        if cpu:
+            cpu.pop("seconds"), cpu.pop("points")
+        line = {"metric": "newton_evals_per_sec", "value": value, "unit": "point*monomials/s",
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"{args.workload}: {desc}", "monomials": int(N), "k": k,
+                           "points_per_gpu": int(P), "parallelism": f"points sharded x{world}",
+                           "l2": "inputs (points) larger than L2, streamed once per step"},
+                "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
+                "roofline": roofline, "cpu_baseline": cpu, "gather_ms": gather_ms,
+                "step_ms": step_ms}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

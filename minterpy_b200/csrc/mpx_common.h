@@ -13,20 +13,22 @@
 // The index set is compiled once per plan into chunks.  One chunk = a fixed-size block of
 // leaf records (descriptor words) plus the coefficient slots those leaves consume, so a CTA
 // can stream chunk after chunk through shared memory with two bulk copies per chunk.
-constexpr int MPX_DESC_WORDS = 512;   // u32 per chunk: [0]=number of words used, [4..] records
+constexpr int MPX_DESC_WORDS = 256;   // u32 per chunk: [0]=number of words used, [4..] records
 constexpr int MPX_DESC_HDR = 4;
-constexpr int MPX_COEF_CAP = 1024;    // coefficient slots (doubles) per chunk and polynomial
-constexpr int MPX_STAGES = 3;         // shared-memory ring depth of the chunk stream
+constexpr int MPX_COEF_CAP = 512;     // coefficient slots (doubles) per chunk and polynomial
+constexpr int MPX_STAGES = 8;         // shared-memory ring depth of the chunk stream
 constexpr int MPX_MAX_L0 = 66;        // dimension-0 table entries a thread can hold in registers
 constexpr int MPX_MAX_M = 16;
 
-// leaf record, one 32-bit word (plus extension words when MPX_D_IRREG is set):
-//   bits 0..5   number of coefficient PAIRS of the leaf (padded length / 2, 1..33)
-//   bits 6..13  exponent of the leaf in dimension 1 (table row of T1)
-//   bits 14..17 nf: how many upper levels (dimensions 2..) receive a fold after this leaf
+// run record, one 32-bit word (plus extension words when MPX_D_IRREG is set).  A RUN is up
+// to 16 consecutive leaves of equal padded length whose dimension-1 exponents count upwards.
+//   bits 0..5   number of coefficient PAIRS of each leaf (padded length / 2, 1..33)
+//   bits 6..13  dimension-1 exponent of the first leaf (table row of T1)
+//   bits 14..17 nf: how many upper levels (dimensions 2..) receive a fold after the run
 //   bit  18     irregular: advance/restart amounts follow in extension words
 //   bits 19..26 exponent of the advancing level before it advances (regular case)
-//   bit  27     last leaf of the program (no advance after the folds)
+//   bit  27     last run of the program (no advance after the folds)
+//   bits 28..31 number of leaves in the run, minus 1
 constexpr uint32_t MPX_D_IRREG = 1u << 18;
 constexpr uint32_t MPX_D_LAST = 1u << 27;
 

@@ -85,6 +85,8 @@ int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_
 
     std::vector<uint32_t> words;   // words of the current chunk (records)
     int coef_used = 0;
+    bool run_open = false;
+    int run_word = 0, run_count = 0, run_lenp = 0, run_e1_next = 0;
     auto flush = [&]() {
         size_t base = pg.desc.size();
         pg.desc.resize(base + MPX_DESC_WORDS, 0u);
@@ -134,10 +136,16 @@ int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_
             }
             pg.other_fp64_per_point += 2;
         }
-        int need_words = 1 + (int)ext.size();
-        if (coef_used + lenp > MPX_COEF_CAP ||
-            (int)words.size() + need_words > MPX_DESC_WORDS - MPX_DESC_HDR)
+        // extend the previous record into a run when this leaf continues it: same padded
+        // length, next dimension-1 exponent, nothing folded in between, same chunk
+        const int cap_words = MPX_DESC_WORDS - MPX_DESC_HDR;
+        const bool fits_coef = coef_used + lenp <= MPX_COEF_CAP;
+        const bool merged = fits_coef && run_open && lenp == run_lenp && e1 == run_e1_next &&
+                            run_count < 16 && (int)(words.size() + ext.size()) <= cap_words;
+        if (!merged && (!fits_coef || (int)(words.size() + 1 + ext.size()) > cap_words)) {
             flush();
+            run_open = false;
+        }
         // coefficient slots of this leaf
         int32_t *slots = pg.slot_src.data() + (size_t)pg.n_chunks * MPX_COEF_CAP + coef_used;
         for (int64_t r = 0; r < lf.count; ++r) {
@@ -145,8 +153,22 @@ int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_
             slots[e[row * m]] = (int32_t)row;
         }
         coef_used += lenp;
-        words.push_back(w);
+        if (merged) {
+            uint32_t &rw = words[run_word];
+            rw = (rw & 0x0fffffffu) | ((uint32_t)run_count << 28);   // leaves in the run - 1
+            rw |= w & 0x0fffc000u;        // fold / advance fields come from the run's last leaf
+            run_count++;
+            run_e1_next = e1 + 1;
+        } else {
+            run_word = (int)words.size();
+            words.push_back(w);
+            run_count = 1;
+            run_lenp = lenp;
+            run_e1_next = e1 + 1;
+        }
         for (uint32_t x : ext) words.push_back(x);
+        // a leaf that folds, advances irregularly or ends the program closes its run
+        run_open = (nf == 0) && !last;
         pg.fma_per_point += lenp + 1 + nf;
     }
     flush();

@@ -11,7 +11,7 @@ import numpy as np
 
 from minterpy_b200 import _lib
 
-DESC_WORDS, DESC_HDR, COEF_CAP = 512, 4, 1024
+DESC_WORDS, DESC_HDR, COEF_CAP = 256, 4, 512
 D_IRREG, D_LAST = 1 << 18, 1 << 27
 
 
@@ -60,14 +60,15 @@ def run_program(desc, slots, x, coeffs, exponents, gp):
         end = DESC_HDR + int(dw[0])
         while i < end:
             w = int(dw[i])
-            np_, e1, nf = w & 63, (w >> 6) & 255, (w >> 14) & 15
-            a = 0.0
-            for s in range(2 * np_ - 1, -1, -1):
-                a += packed[cp + s] * T0[s]
+            np_, e1, nf, count = w & 63, (w >> 6) & 255, (w >> 14) & 15, (w >> 28) + 1
+            for j in range(count):           # a run: equal-length leaves, e1 counting upwards
+                a = 0.0
+                for s in range(2 * np_ - 1, -1, -1):
+                    a += packed[cp + s] * T0[s]
+                    fma += 1
+                cp += 2 * np_
+                acc1 += T1[e1 + j] * a
                 fma += 1
-            cp += 2 * np_
-            acc1 += T1[e1] * a
-            fma += 1
             if nf:
                 adv, cur = 1, (w >> 19) & 255
                 irregular, last = bool(w & D_IRREG), bool(w & D_LAST)

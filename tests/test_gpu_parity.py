@@ -1,0 +1,267 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the golden vectors written
+by the unmodified reference and against the CPU oracle.
+
+Tolerances (stated once, used everywhere):
+  * polynomial values: max|gpu - ref| <= EVAL_RTOL * max|ref|, EVAL_RTOL = 1e-13
+    (the contract in BASELINE.json is 1e-12; the reference's own BLAS product is only
+    defined up to summation order);
+  * Newton monomials and divided differences: bit-exact.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+import golden_io
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+EVAL_RTOL = 1e-13
+SMALL_TAGS = [f"m{m}_n{n}_lp{lp}" for m in (1, 2, 3) for n in (0, 1, 4)
+              for lp in (0.5, 1.0, 2.0, np.inf)]
+CFGS = ["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"]
+
+
+@pytest.fixture(scope="module")
+def mpb():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import minterpy_b200
+    return minterpy_b200
+
+
+def rel_err(a, ref):
+    scale = np.max(np.abs(ref))
+    return np.max(np.abs(np.asarray(a) - ref)) / (scale if scale > 0 else 1.0)
+
+
+@pytest.mark.parametrize("tag", SMALL_TAGS)
+def test_small_golden(mpb, golden_small, tag):
+    g = golden_small
+    e, gp, xx = g[f"{tag}/exponents"], g[f"{tag}/generating_points"], g[f"{tag}/xx"]
+    plan = mpb.get_plan(e, gp)
+    for k in (1, 10):
+        ev = plan.eval(xx, g[f"{tag}/k{k}/coeffs"])
+        assert rel_err(ev, g[f"{tag}/k{k}/eval_ref"]) <= EVAL_RTOL
+        out = plan.dds(g[f"{tag}/k{k}/dds_in"])
+        assert np.array_equal(out, g[f"{tag}/k{k}/dds_ref"])
+    mono = plan.monomials(xx)
+    assert np.array_equal(mono, g[f"{tag}/monomials_ref"])
+    tri = plan.monomials(g[f"{tag}/unisolvent_nodes"], triangular=True)
+    assert np.array_equal(tri, g[f"{tag}/monomials_tri_ref"])
+
+
+@pytest.mark.parametrize("tag", CFGS)
+def test_config_eval_golden(mpb, golden_cfg, tag):
+    g = golden_cfg(tag)
+    e, gp = g["exponents"], g["generating_points"]
+    k = int(g["k_eval"])
+    c = golden_io.seeded(g, "coeffs_seed", "coeffs_sha", (e.shape[0], k))
+    ev = mpb.get_plan(e, gp).eval(g["xx"], c)
+    assert rel_err(ev, g["eval_ref"]) <= EVAL_RTOL
+
+
+@pytest.mark.parametrize("tag", CFGS)
+def test_config_dds_golden_bit_exact(mpb, golden_cfg, tag):
+    g = golden_cfg(tag)
+    e, gp = g["exponents"], g["generating_points"]
+    plan = mpb.get_plan(e, gp)
+    ref = g["dds_ref"]
+    vals = golden_io.seeded(g, "dds_seed", "dds_in_sha", ref.shape)
+    assert np.array_equal(plan.dds(vals), ref)
+    assert np.array_equal(plan.dds(g["smooth_in"].reshape(-1, 1)), g["smooth_dds_ref"])
+
+
+def test_cfg4_wide_dds_hash(mpb, golden_cfg):
+    """BASELINE config 4 at full size: 59 711 x 256 values, bit-exact through a sha256."""
+    g = golden_cfg("cfg4")
+    e, gp = g["exponents"], g["generating_points"]
+    wide = golden_io.seeded(g, "dds_wide_seed", "dds_wide_in_sha", (e.shape[0], 256))
+    out = mpb.get_plan(e, gp).dds(wide)
+    assert golden_io.sha256_of(out) == str(g["dds_wide_ref_sha"])
+
+
+def test_quickstart(mpb, golden_cfg):
+    """README quickstart: interpolate x sin(10x) with degree 64, evaluate at 1e6 points."""
+    g = golden_cfg("cfg1")
+    mi = mpb.MultiIndexSet(g["exponents"])
+    grid = mpb.Grid(mi, g["generating_points"])
+    poly = mpb.interpolate(lambda x: (x * np.sin(10 * x)).reshape(-1), grid)
+    assert np.array_equal(poly.coeffs, g["quickstart_coeffs"])
+    y = poly(np.linspace(-1, 1, 1_000_000))
+    assert y.shape == (1_000_000,)
+    assert rel_err(y[::1000], g["quickstart_every1000"]) <= EVAL_RTOL
+
+
+def test_against_oracle_irregular_sets(mpb):
+    """Unsorted index sets with holes: evaluation must not depend on completeness."""
+    rng = np.random.default_rng(11)
+    for trial in range(12):
+        m = int(rng.integers(1, 6))
+        N = int(rng.integers(1, 200))
+        e = np.unique(rng.integers(0, 9, (N, m)), axis=0).astype(np.int64)
+        rng.shuffle(e)
+        gp = rng.uniform(-1, 1, (10, m))
+        k = int(rng.integers(1, 4))
+        c = rng.uniform(-1, 1, (e.shape[0], k))
+        xx = rng.uniform(-1, 1, (37, m))
+        plan = mpb.Plan(e, gp)
+        assert rel_err(plan.eval(xx, c), oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL
+        assert np.array_equal(plan.monomials(xx), oracle.eval_newton_monomials(xx, e, gp))
+        if not plan.is_complete:
+            with pytest.raises(ValueError):
+                plan.dds(np.ones((e.shape[0], 1)))
+
+
+@pytest.mark.parametrize("P", [0, 1, 255, 256, 511, 513, 1025])
+def test_ragged_point_counts(mpb, golden_cfg, P):
+    g = golden_cfg("cfg2")
+    e, gp = g["exponents"][:500], g["generating_points"]      # a lexicographic prefix is complete
+    rng = np.random.default_rng(P)
+    c = rng.uniform(-1, 1, (e.shape[0], 2))
+    xx = rng.uniform(-1, 1, (P, 4))
+    out = mpb.get_plan(e, gp).eval(xx, c)
+    assert out.shape == (P, 2)
+    if P:
+        assert rel_err(out, oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL
+
+
+def test_device_path_matches_host_path_and_strides(mpb, golden_cfg):
+    import torch
+    g = golden_cfg("cfg3")
+    e, gp = g["exponents"], g["generating_points"]
+    rng = np.random.default_rng(3)
+    N, m = e.shape
+    c = rng.uniform(-1, 1, (N, 5))
+    xx = rng.uniform(-1, 1, (300, m))
+    plan = mpb.get_plan(e, gp)
+    host = plan.eval(xx, c)
+    # zero-copy torch path with non-trivial leading dimensions
+    xt = torch.zeros((300, m + 3), dtype=torch.float64, device="cuda")
+    xt[:, :m] = torch.from_numpy(xx).cuda()
+    ct = torch.zeros((N, 8), dtype=torch.float64, device="cuda")
+    ct[:, :5] = torch.from_numpy(c).cuda()
+    dev = plan.eval(xt[:, :m], ct[:, :5])
+    assert dev.is_cuda and dev.shape == (300, 5)
+    assert np.array_equal(dev.cpu().numpy(), host)
+    assert rel_err(host, oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL
+    # dds on a CUDA tensor: result on the device, input untouched
+    vt = torch.from_numpy(c).cuda()
+    keep = vt.clone()
+    dt = plan.dds(vt)
+    assert torch.equal(vt, keep)
+    assert np.array_equal(dt.cpu().numpy(), oracle.dds(c, e, gp))
+
+
+def test_api_shapes_and_errors(mpb, golden_small):
+    """Shape, squeeze and error rules of src/minterpy/core/verification.py:48-163."""
+    g = golden_small
+    tag = "m3_n4_lp2.0"
+    e, gp = g[f"{tag}/exponents"], g[f"{tag}/generating_points"]
+    N = e.shape[0]
+    c1, c10 = g[f"{tag}/k1/coeffs"][:, 0], g[f"{tag}/k10/coeffs"]
+    xx = g[f"{tag}/xx"]
+    f = mpb.eval_newton_polynomials
+    assert f(xx, c1, e, gp).shape == (xx.shape[0],)
+    assert f(xx, c10, e, gp).shape == (xx.shape[0], 10)
+    assert f(xx[0], c10, e, gp).shape == (10,)              # 1-D x with m > 1: one point
+    assert f(xx[0], c1, e, gp).shape == (1,)                # never 0-D
+    assert f(xx[:1], c1.reshape(N, 1), e, gp).shape == (1,)
+    for bs in (1, 100, 1000):                               # batch_size must not change results
+        assert np.array_equal(f(xx, c10, e, gp, batch_size=bs), f(xx, c10, e, gp))
+    with pytest.raises(ValueError):
+        f(xx[:, :2], c1, e, gp)                             # wrong point dimension
+    with pytest.raises(ValueError):
+        f(xx[0, :2], c1, e, gp)
+    with pytest.raises(ValueError):
+        f(xx, c10[:-1], e, gp)                              # coefficient count mismatch
+    with pytest.raises(ValueError):
+        f(xx, c1[:0], e[:0], gp)                            # no monomials
+    with pytest.raises(TypeError):
+        f(xx.astype(np.float32), c1, e, gp)
+    with pytest.raises(TypeError):
+        f(xx, c1, e.astype(np.int32), gp)
+    # m == 1: a 1-D x is a list of points
+    e1, gp1 = g["m1_n4_lp2.0/exponents"], g["m1_n4_lp2.0/generating_points"]
+    assert f(np.linspace(-1, 1, 7), np.ones(5), e1, gp1).shape == (7,)
+    # dds: 1-D input -> (N, 1); works on a copy
+    tree = mpb.Grid(mpb.MultiIndexSet(e), gp).tree
+    vals = g[f"{tag}/k1/dds_in"][:, 0].copy()
+    keep = vals.copy()
+    out = mpb.dds(vals, tree)
+    assert out.shape == (N, 1) and np.array_equal(vals, keep)
+    assert np.array_equal(out, g[f"{tag}/k1/dds_ref"])
+
+
+def test_transformations_round_trip(mpb, golden_small):
+    """LagrangeToNewton / NewtonToLagrange against the reference's operators, and
+    back-and-forth identity (tests/test_transformation.py:119-173,197-208)."""
+    g = golden_small
+    for tag in ("m3_n4_lp2.0", "m2_n4_lpinf", "m1_n4_lp1.0", "m3_n1_lp0.5", "m3_n0_lp2.0"):
+        e, gp = g[f"{tag}/exponents"], g[f"{tag}/generating_points"]
+        mi = mpb.MultiIndexSet(e)
+        grid = mpb.Grid(mi, gp)
+        assert np.array_equal(grid.unisolvent_nodes, g[f"{tag}/unisolvent_nodes"])
+        for k in (1, 10):
+            lag_c = g[f"{tag}/k{k}/dds_in"] if k > 1 else g[f"{tag}/k{k}/dds_in"][:, 0]
+            lag = mpb.LagrangePolynomial(mi, lag_c, grid=grid)
+            newt = mpb.LagrangeToNewton(lag)()
+            assert isinstance(newt, mpb.NewtonPolynomial) and newt.coeffs.shape == lag_c.shape
+            assert rel_err(newt.coeffs.reshape(len(mi), k), g[f"{tag}/k{k}/l2n_ref"]) <= 1e-12
+            back = mpb.NewtonToLagrange(newt)()
+            assert rel_err(back.coeffs, lag_c) <= 1e-12
+            nc = g[f"{tag}/k{k}/coeffs"] if k > 1 else g[f"{tag}/k{k}/coeffs"][:, 0]
+            n2l = mpb.NewtonToLagrange(mpb.NewtonPolynomial(mi, nc, grid=grid))()
+            assert rel_err(n2l.coeffs.reshape(len(mi), k), g[f"{tag}/k{k}/n2l_ref"]) <= EVAL_RTOL
+        op = mpb.LagrangeToNewton(lag).transformation_operator
+        n2l_op = mpb.NewtonToLagrange(newt).transformation_operator
+        assert rel_err(op.array_repr_full @ n2l_op.array_repr_full, np.eye(len(mi))) <= 1e-10
+
+
+def test_large_properties_cfg2(mpb, golden_cfg):
+    """BASELINE config 2 at a size the oracle cannot reach in seconds: size-independent
+    properties -- linearity in the coefficients, and interpolation reproducing a polynomial
+    (tests/test_interpolation.py:71-105)."""
+    import torch
+    g = golden_cfg("cfg2")
+    e, gp = g["exponents"], g["generating_points"]
+    N, m = e.shape
+    plan = mpb.get_plan(e, gp)
+    gen = torch.Generator(device="cuda").manual_seed(20261106)
+    P = 1 << 20
+    xx = torch.rand((P, m), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+    c = torch.rand((N, 2), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+    y = plan.eval(xx, c)
+    ysum = plan.eval(xx, (c[:, 0] + 0.5 * c[:, 1]).reshape(N, 1))
+    scale = y.abs().max().item()
+    assert (ysum[:, 0] - (y[:, 0] + 0.5 * y[:, 1])).abs().max().item() <= 1e-12 * scale
+    # spot-check 64 of the 2^20 points against the oracle
+    idx = torch.randint(0, P, (64,), generator=gen, device="cuda")
+    ref = oracle.eval_newton_polynomials(xx[idx].cpu().numpy(), c.cpu().numpy(), e, gp, nthreads=4)
+    assert rel_err(y[idx].cpu().numpy(), ref) <= EVAL_RTOL
+    # round trip: values at the unisolvent nodes -> dds -> the same coefficients
+    grid = mpb.Grid(mpb.MultiIndexSet(e), gp)
+    nodes = torch.from_numpy(grid.unisolvent_nodes).cuda()
+    lag = plan.eval(nodes, c)
+    back = plan.dds(lag)
+    # dds at N = 24 809 amplifies rounding errors of its input by ~1e8 (the oracle shows the
+    # same loss on the same values), so the round trip is a coarse check ...
+    assert (back - c).abs().max().item() <= 1e-5 * c.abs().max().item()
+    # ... and the sharp one is bit-exactness against the oracle on those values
+    assert np.array_equal(back.cpu().numpy(), oracle.dds(lag.cpu().numpy(), e, gp))
+
+
+def test_dense_apply(mpb):
+    import torch
+    from minterpy_b200 import _lib
+    rng = np.random.default_rng(2)
+    for rows, cols, k in ((1, 1, 1), (70, 70, 1), (130, 97, 5), (513, 513, 9)):
+        T = np.tril(rng.uniform(-1, 1, (rows, cols)))
+        c = rng.uniform(-1, 1, (cols, k))
+        Tt, ct = torch.from_numpy(T).cuda(), torch.from_numpy(c).cuda()
+        out = torch.empty((rows, k), dtype=torch.float64, device="cuda")
+        rc = _lib.lib().mpx_apply_dense(0, Tt.data_ptr(), rows, cols, cols, ct.data_ptr(), k, k,
+                                        out.data_ptr(), k, None)
+        _lib.check(rc)
+        assert rel_err(out.cpu().numpy(), T @ c) <= 1e-13
