@@ -20,17 +20,26 @@ constexpr int MPX_STAGES = 8;         // shared-memory ring depth of the chunk s
 constexpr int MPX_MAX_L0 = 66;        // dimension-0 table entries a thread can hold in registers
 constexpr int MPX_MAX_M = 16;
 
-// run record, one 32-bit word (plus extension words when MPX_D_IRREG is set).  A RUN is up
-// to 16 consecutive leaves of equal padded length whose dimension-1 exponents count upwards.
-//   bits 0..5   number of coefficient PAIRS of each leaf (padded length / 2, 1..33)
-//   bits 6..13  dimension-1 exponent of the first leaf (table row of T1)
-//   bits 14..17 nf: how many upper levels (dimensions 2..) receive a fold after the run
-//   bit  18     irregular: advance/restart amounts follow in extension words
-//   bits 19..26 exponent of the advancing level before it advances (regular case)
-//   bit  27     last run of the program (no advance after the folds)
-//   bits 28..31 number of leaves in the run, minus 1
-constexpr uint32_t MPX_D_IRREG = 1u << 18;
-constexpr uint32_t MPX_D_LAST = 1u << 27;
+// Record = one header word, MPX count words, then extension words when MPX_D_IRREG is set.
+// A record covers consecutive leaves (dimension-1 exponent counting upwards from e1_first)
+// whose padded lengths do not increase; the count words say how many of them have K
+// coefficient pairs, 4 bits per K (K = 1 in the lowest nibble), at most 15 each.  The kernel
+// walks K downwards through straight-line code specialised for each K.
+//   header bits 0..7   dimension-1 exponent of the first leaf (table row of T1)
+//          bits 8..11  nf: how many upper levels (dimensions 2..) receive a fold afterwards
+//          bit  12     irregular: advance/restart amounts follow in extension words
+//          bit  13     last record of the program (no advance after the folds)
+//          bits 14..21 exponent of the advancing level before it advances (regular case)
+constexpr uint32_t MPX_D_IRREG = 1u << 12;
+constexpr uint32_t MPX_D_LAST = 1u << 13;
+
+// kernel variant = size of the dimension-0 register table (even, >= max exponent + 1)
+inline int mpx_l0p_for(int max_exp0)
+{
+    const int L0 = max_exp0 + 1;
+    return L0 <= 10 ? 10 : L0 <= 18 ? 18 : L0 <= 34 ? 34 : 66;
+}
+inline int mpx_count_words(int l0p) { return (l0p / 2 + 7) / 8; }
 
 struct EvalProgram {
     int n_chunks = 0;

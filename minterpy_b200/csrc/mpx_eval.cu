@@ -126,100 +126,117 @@ __device__ __forceinline__ double lds64(uint32_t addr)
     return v;
 }
 
-// One run: `cnt` leaves of K coefficient pairs each, dimension-1 exponents counting upwards.
-// K is a compile-time constant here, so the body is straight-line code: K broadcast loads of
-// coefficient pairs, R loads of T1, 2K FMAs per point into A independent accumulators
-// (A = 2: odd and even monomials apart, twice the independent chains), then one FMA per
-// point into the level-1 sum.  Highest monomial first, as a Duff-style entry would do.
-template <int L0P, int R, int A, int K>
-struct Run {
-    static __device__ __forceinline__ void go(double (&acc1)[R], const double (&T0)[R][L0P],
-                                              uint32_t cp, uint32_t t1a, int cnt,
-                                              uint32_t t1_row_bytes, uint32_t t1_r_bytes)
+// T1 (dimension-1 table) in shared memory.  R even: [e][r/2][thread][r%2], so one LDS.128
+// fetches the values of two points (lane stride 16 B, conflict free); R odd: [e][r][thread].
+template <int R, int NT>
+struct T1Layout {
+    static constexpr bool PAIRED = (R % 2 == 0);
+    static constexpr uint32_t ROW_BYTES = (uint32_t)R * NT * 8u;
+    static __device__ __forceinline__ uint32_t index(int e, int r, int tid)
     {
-#pragma unroll 1
-        for (int j = 0; j < cnt; ++j) {
-            double2 cf[K];
+        if constexpr (PAIRED) return ((uint32_t)(e * (R / 2) + r / 2) * NT + tid) * 2 + (r & 1);
+        else return (uint32_t)(e * R + r) * NT + tid;
+    }
+    static __device__ __forceinline__ uint32_t lane_base(uint32_t t1s_addr, int tid)
+    {
+        return t1s_addr + (uint32_t)tid * (PAIRED ? 16u : 8u);
+    }
+    static __device__ __forceinline__ void load(double (&v)[R], uint32_t row_addr)
+    {
+        if constexpr (PAIRED) {
 #pragma unroll
-            for (int i = 0; i < K; ++i) cf[i] = lds128(cp + 16 * i);
-            double t1v[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r) t1v[r] = lds64(t1a + r * t1_r_bytes);
-            double a[R][A];
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if constexpr (A == 2) {
-                    a[r][1] = cf[K - 1].y * T0[r][2 * K - 1];
-                    a[r][0] = cf[K - 1].x * T0[r][2 * K - 2];
-                } else {
-                    a[r][0] = fma(cf[K - 1].x, T0[r][2 * K - 2], cf[K - 1].y * T0[r][2 * K - 1]);
-                }
+            for (int h = 0; h < R / 2; ++h) {
+                const double2 t = lds128(row_addr + (uint32_t)h * NT * 16u);
+                v[2 * h] = t.x;
+                v[2 * h + 1] = t.y;
             }
+        } else {
 #pragma unroll
-            for (int i = K - 2; i >= 0; --i) {
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    a[r][A - 1] = fma(cf[i].y, T0[r][2 * i + 1], a[r][A - 1]);
-                    a[r][0] = fma(cf[i].x, T0[r][2 * i], a[r][0]);
-                }
-            }
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if constexpr (A == 2) acc1[r] = fma(t1v[r], a[r][0] + a[r][1], acc1[r]);
-                else acc1[r] = fma(t1v[r], a[r][0], acc1[r]);
-            }
-            cp += 16 * K;
-            t1a += t1_row_bytes;
+            for (int r = 0; r < R; ++r) v[r] = lds64(row_addr + (uint32_t)r * NT * 8u);
         }
     }
 };
 
-#define MPX_RUN_CASE(K)                                                                        \
-    case (K):                                                                                  \
-        if constexpr ((K) <= L0P / 2)                                                          \
-            Run<L0P, R, A, ((K) <= L0P / 2 ? (K) : 1)>::go(acc1, T0, cp, t1a, cnt, t1_row_bytes, \
-                                                           t1_r_bytes);                        \
-        break;
-
-template <int L0P, int R, int A>
-__device__ __forceinline__ void run_dispatch(double (&acc1)[R], const double (&T0)[R][L0P],
-                                             uint32_t cp, uint32_t t1a, int np, int cnt,
-                                             uint32_t t1_row_bytes, uint32_t t1_r_bytes)
+// `cnt` consecutive leaves of K coefficient pairs each (dimension-1 exponent counting up).
+// K is a compile-time constant, so the body is straight-line code: K broadcast loads of
+// coefficient pairs, the T1 values of the R points, 2K FMAs per point into A independent
+// accumulators (A = 2: odd and even monomials apart), then one FMA per point into the
+// level-1 sum.  Highest monomial first.
+template <int L0P, int R, int A, int NT, int K>
+__device__ __forceinline__ void run_leaves(double (&acc1)[R], const double (&T0)[R][L0P],
+                                           uint32_t &cp, uint32_t &t1a, int cnt)
 {
-    switch (np) {
-        MPX_RUN_CASE(1) MPX_RUN_CASE(2) MPX_RUN_CASE(3) MPX_RUN_CASE(4) MPX_RUN_CASE(5)
-        MPX_RUN_CASE(6) MPX_RUN_CASE(7) MPX_RUN_CASE(8) MPX_RUN_CASE(9) MPX_RUN_CASE(10)
-        MPX_RUN_CASE(11) MPX_RUN_CASE(12) MPX_RUN_CASE(13) MPX_RUN_CASE(14) MPX_RUN_CASE(15)
-        MPX_RUN_CASE(16) MPX_RUN_CASE(17) MPX_RUN_CASE(18) MPX_RUN_CASE(19) MPX_RUN_CASE(20)
-        MPX_RUN_CASE(21) MPX_RUN_CASE(22) MPX_RUN_CASE(23) MPX_RUN_CASE(24) MPX_RUN_CASE(25)
-        MPX_RUN_CASE(26) MPX_RUN_CASE(27) MPX_RUN_CASE(28) MPX_RUN_CASE(29) MPX_RUN_CASE(30)
-        MPX_RUN_CASE(31) MPX_RUN_CASE(32) MPX_RUN_CASE(33)
-    default:
-        break;
-    }
+    const uint32_t cp_end = cp + (uint32_t)cnt * (16u * K);
+#pragma unroll 1
+    do {
+        double2 cf[K];
+#pragma unroll
+        for (int i = 0; i < K; ++i) cf[i] = lds128(cp + 16 * i);
+        double t1v[R];
+        T1Layout<R, NT>::load(t1v, t1a);
+        double a[R][A];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if constexpr (A == 2) {
+                a[r][1] = cf[K - 1].y * T0[r][2 * K - 1];
+                a[r][0] = cf[K - 1].x * T0[r][2 * K - 2];
+            } else {
+                a[r][0] = fma(cf[K - 1].x, T0[r][2 * K - 2], cf[K - 1].y * T0[r][2 * K - 1]);
+            }
+        }
+#pragma unroll
+        for (int i = K - 2; i >= 0; --i) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                a[r][A - 1] = fma(cf[i].y, T0[r][2 * i + 1], a[r][A - 1]);
+                a[r][0] = fma(cf[i].x, T0[r][2 * i], a[r][0]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            if constexpr (A == 2) acc1[r] = fma(t1v[r], a[r][0] + a[r][1], acc1[r]);
+            else acc1[r] = fma(t1v[r], a[r][0], acc1[r]);
+        }
+        cp += 16 * K;
+        t1a += T1Layout<R, NT>::ROW_BYTES;
+    } while (cp != cp_end);
 }
+
+// walk the lengths of one record downwards: K = L0P/2, ..., 1
+template <int L0P, int R, int A, int NT, int K>
+struct LengthChain {
+    static __device__ __forceinline__ void go(double (&acc1)[R], const double (&T0)[R][L0P],
+                                              uint32_t &cp, uint32_t &t1a,
+                                              const uint32_t (&counts)[(L0P / 2 + 7) / 8])
+    {
+        const int cnt = (int)((counts[(K - 1) / 8] >> (4 * ((K - 1) % 8))) & 15u);
+        if (cnt) run_leaves<L0P, R, A, NT, K>(acc1, T0, cp, t1a, cnt);
+        if constexpr (K > 1) LengthChain<L0P, R, A, NT, K - 1>::go(acc1, T0, cp, t1a, counts);
+    }
+};
 
 // shared-memory carve-up (dynamic):
 //   [0, 128)                     mbarriers: full[], empty[]
 //   [128, 128 + S*STAGE_BYTES)   ring: per stage desc words then coefficients
 //   then gp (m*gp_rows doubles), T1 ((max_exp1+1)*R*NT doubles),
-//   upper-level state product/sum/coordinate (3 * U * R * NT doubles)
-template <int L0P, int R, int A, int MINB>
-__global__ void __launch_bounds__(256, MINB) eval_tree_kernel(const EvalParams p)
+//   upper-level state running product / partial sum (2 * U * R * NT doubles)
+template <int L0P, int R, int A, int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
 {
     extern __shared__ __align__(128) unsigned char smem[];
+    constexpr int NCW = (L0P / 2 + 7) / 8;
+    using T1L = T1Layout<R, NT>;
     const int tid = threadIdx.x;
-    const int NT = blockDim.x;
     const int m = p.m;
     const int U = m > 2 ? m - 2 : 0;
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem);
     const int S = p.stages;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem);
     uint64_t *empty = full + MPX_STAGES;
     unsigned char *ring = smem + 128;
     double *gps = reinterpret_cast<double *>(ring + S * STAGE_BYTES);
     double *T1s = gps + ((m * p.gp_rows + 1) & ~1);
     const int me1 = (m >= 2) ? p.max_exp[1] : 0;
-    double *ups = T1s + (size_t)(me1 + 1) * R * NT;   // [3][U][R][NT]: product, sum, coordinate
+    double *ups = T1s + (size_t)(me1 + 1) * R * NT;   // [2][U][R][NT]: running product, sum
     const size_t up_stride = (size_t)U * R * NT;
 
     const int q = blockIdx.y;                                   // polynomial
@@ -234,7 +251,8 @@ __global__ void __launch_bounds__(256, MINB) eval_tree_kernel(const EvalParams p
     }
     for (int i = tid; i < m * p.gp_rows; i += NT) gps[i] = p.gp[i];
     __syncthreads();
-    // Producer = thread 0, never blocking: it tops the ring up whenever it polls a stage free.
+    // Producer = thread 0, never blocking unless it must: it tops the ring up at every chunk
+    // boundary with whatever stages all threads have released by then.
     int next_load = 0;
     auto issue_load = [&](int cn) {
         const int sp = cn % S;
@@ -255,28 +273,28 @@ __global__ void __launch_bounds__(256, MINB) eval_tree_kernel(const EvalParams p
     const int64_t tile0 = (int64_t)blockIdx.x * (R * NT);
     double T0[R][L0P];
     double acc1[R];
+    const double *xrow[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         int64_t pt = tile0 + (int64_t)r * NT + tid;
         if (pt >= p.P) pt = p.P - 1;               // tail threads recompute the last point
         const double *xp = p.xx + pt * p.ld_xx;
+        xrow[r] = xp;
         const double x0 = xp[0];
         const int me0 = p.max_exp[0];
         T0[r][0] = 1.0;
 #pragma unroll
         for (int j = 0; j < L0P - 1; ++j)
             T0[r][j + 1] = (j < me0) ? T0[r][j] * (x0 - gps[j]) : 0.0;
+        T1s[T1L::index(0, r, tid)] = 1.0;
         if (m >= 2) {
             const double x1 = xp[1];
             double prod = 1.0;
-            T1s[(size_t)r * NT + tid] = 1.0;
 #pragma unroll 1
             for (int j = 0; j < me1; ++j) {
                 prod *= x1 - gps[p.gp_rows + j];
-                T1s[((size_t)(j + 1) * R + r) * NT + tid] = prod;
+                T1s[T1L::index(j + 1, r, tid)] = prod;
             }
-        } else {
-            T1s[(size_t)r * NT + tid] = 1.0;
         }
 #pragma unroll 1
         for (int u = 0; u < U; ++u) {
@@ -287,57 +305,56 @@ __global__ void __launch_bounds__(256, MINB) eval_tree_kernel(const EvalParams p
             const size_t o = ((size_t)u * R + r) * NT + tid;
             ups[o] = t;
             ups[up_stride + o] = 0.0;
-            ups[2 * up_stride + o] = xu;
         }
         acc1[r] = 0.0;
     }
-    // (each thread only ever touches its own T1s / ups columns: no barrier needed)
-    const uint32_t t1_base = smem_u32(T1s + tid);
-    const uint32_t t1_r_bytes = (uint32_t)NT * 8u;            // T1 is [e][r][thread]
-    const uint32_t t1_row_bytes = (uint32_t)R * t1_r_bytes;
+    // (each thread only ever touches its own T1s / ups entries: no barrier needed)
+    const uint32_t t1_base = T1L::lane_base(smem_u32(T1s), tid);
 
     // ---- stream the program -------------------------------------------------------------
     for (int c = 0; c < p.n_chunks; ++c) {
         const int s = c % S;
         const uint32_t ph = (uint32_t)(c / S) & 1u;
-        while (next_load <= c) {
-            // thread 0, rare: chunk c itself was never requested because the stage it needs
-            // was still in use at every poll -- now it has to wait for that stage
-            const int sp = next_load % S;
-            mbar_wait(&empty[sp], (uint32_t)(next_load / S - 1) & 1u);
-            issue_load(next_load);
-            ++next_load;
+        if (next_load < p.n_chunks) {
+            // thread 0: refill every stage that all threads have released; if chunk c itself
+            // has not been requested yet (its stage was busy at every earlier poll), wait.
+            for (;;) {
+                const int sp = next_load % S;
+                const uint32_t php = (uint32_t)(next_load / S - 1) & 1u;
+                if (next_load <= c) mbar_wait(&empty[sp], php);
+                else if (!mbar_test(&empty[sp], php)) break;
+                issue_load(next_load);
+                if (++next_load >= p.n_chunks) break;
+            }
         }
         mbar_wait(&full[s], ph);
         const uint32_t *dw = reinterpret_cast<const uint32_t *>(ring + s * STAGE_BYTES);
         uint32_t cp = smem_u32(ring + s * STAGE_BYTES + MPX_DESC_WORDS * 4);
         const int iend = MPX_DESC_HDR + (int)dw[0];
-        uint32_t w = dw[MPX_DESC_HDR];
-        for (int i = MPX_DESC_HDR; i < iend; ++i) {
-            if ((i & 7) == 0 && next_load < p.n_chunks) {
-                // thread 0 only: refill the oldest stage if every thread has released it
-                const int sp = next_load % S;
-                const uint32_t php = (uint32_t)(next_load / S - 1) & 1u;
-                if (mbar_test(&empty[sp], php)) {
-                    issue_load(next_load);
-                    ++next_load;
-                }
+        for (int i = MPX_DESC_HDR; i < iend;) {
+            const uint32_t w = dw[i];
+            uint32_t counts[NCW];
+#pragma unroll
+            for (int z = 0; z < NCW; ++z) counts[z] = dw[i + 1 + z];
+            i += 1 + NCW;
+            const int e1 = w & 255;
+            const int nf = (w >> 8) & 15;
+            // a fold follows this record: fetch the coordinate of the level that will advance
+            // now (L1/L2 hit), so the load is hidden behind the record's FMAs
+            double xadv[R];
+            if (nf) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) xadv[r] = __ldg(xrow[r] + 1 + nf);
             }
-            uint32_t w_next = dw[i + 1];     // next record, fetched a whole run ahead
-            const int np = w & 63;
-            const int e1 = (w >> 6) & 255;
-            const int nf = (w >> 14) & 15;
-            const int cnt = (int)(w >> 28) + 1;
-            run_dispatch<L0P, R, A>(acc1, T0, cp, t1_base + (uint32_t)e1 * t1_row_bytes, np, cnt,
-                                    t1_row_bytes, t1_r_bytes);
-            cp += 16 * np * cnt;
+            uint32_t t1a = t1_base + (uint32_t)e1 * T1L::ROW_BYTES;
+            LengthChain<L0P, R, A, NT, L0P / 2>::go(acc1, T0, cp, t1a, counts);
             if (nf) {
                 // fold finished subtrees upwards: levels 0..nf-1 (dimensions 2..nf+1)
-                int adv = 1, cur = (w >> 19) & 255;
+                int adv = 1, cur = (w >> 14) & 255;
                 const bool irregular = (w & MPX_D_IRREG) != 0;
                 const bool last = (w & MPX_D_LAST) != 0;
                 if (irregular) {
-                    const uint32_t x = dw[++i];
+                    const uint32_t x = dw[i];
                     cur = x & 255;
                     adv = (int)(x >> 8);
                 }
@@ -348,45 +365,60 @@ __global__ void __launch_bounds__(256, MINB) eval_tree_kernel(const EvalParams p
                     acc1[r] = 0.0;
                 }
 #pragma unroll 1
-                for (int u = 0; u < nf; ++u) {
+                for (int u = 0; u < nf - 1; ++u) {
+                    // level complete as well: hand its sum upwards and restart it
                     double *ut = ups + (size_t)u * R * NT + tid;
-                    if (u < nf - 1) {
-                        // level complete as well: hand its sum upwards and restart it
-                        const int st = irregular ? (int)dw[i + 1 + u] : 0;
+                    double tv[R], av[R];
 #pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            low[r] = fma(ut[r * NT], low[r], ut[up_stride + r * NT]);
-                            ut[up_stride + r * NT] = 0.0;
-                            double tn = 1.0;
-                            if (st) {
-                                const double xu = ut[2 * up_stride + r * NT];
-#pragma unroll 1
-                                for (int j = 0; j < st; ++j) tn *= xu - gps[(2 + u) * p.gp_rows + j];
-                            }
-                            ut[r * NT] = tn;
-                        }
-                    } else {
+                    for (int r = 0; r < R; ++r) {
+                        tv[r] = ut[r * NT];
+                        av[r] = ut[up_stride + r * NT];
+                    }
+                    const int st = irregular ? (int)dw[i + 1 + u] : 0;
 #pragma unroll
-                        for (int r = 0; r < R; ++r) {
-                            double t = ut[r * NT];
-                            ut[up_stride + r * NT] = fma(t, low[r], ut[up_stride + r * NT]);
-                            if (!last) {
-                                const double xu = ut[2 * up_stride + r * NT];
-                                t *= xu - gps[(2 + u) * p.gp_rows + cur];
+                    for (int r = 0; r < R; ++r) {
+                        low[r] = fma(tv[r], low[r], av[r]);
+                        double tn = 1.0;
+                        if (st) {
+                            const double xu = xrow[r][2 + u];
 #pragma unroll 1
-                                for (int j = 1; j < adv; ++j)
-                                    t *= xu - gps[(2 + u) * p.gp_rows + cur + j];
-                                ut[r * NT] = t;
-                            }
+                            for (int j = 0; j < st; ++j) tn *= xu - gps[(2 + u) * p.gp_rows + j];
                         }
+                        ut[up_stride + r * NT] = 0.0;
+                        ut[r * NT] = tn;
                     }
                 }
-                if (irregular) {
-                    i += nf - 1;
-                    w_next = dw[i + 1];
+                {
+                    const int u = nf - 1;
+                    double *ut = ups + (size_t)u * R * NT + tid;
+                    const double g = gps[(2 + u) * p.gp_rows + cur];
+                    double tv[R], av[R];
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        tv[r] = ut[r * NT];
+                        av[r] = ut[up_stride + r * NT];
+                    }
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        av[r] = fma(tv[r], low[r], av[r]);
+                        tv[r] *= xadv[r] - g;
+                    }
+                    if (adv > 1) {
+#pragma unroll 1
+                        for (int j = 1; j < adv; ++j) {
+                            const double gj = gps[(2 + u) * p.gp_rows + cur + j];
+#pragma unroll
+                            for (int r = 0; r < R; ++r) tv[r] *= xadv[r] - gj;
+                        }
+                    }
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        ut[up_stride + r * NT] = av[r];
+                        if (!last) ut[r * NT] = tv[r];
+                    }
                 }
+                if (irregular) i += nf;
             }
-            w = w_next;
         }
         mbar_arrive(&empty[s]);
     }
@@ -408,10 +440,10 @@ struct Variant {
     const void *fn;
 };
 
-template <int L0P, int R, int A, int MINB>
+template <int L0P, int R, int A, int NT, int MINB>
 const void *kfn()
 {
-    return reinterpret_cast<const void *>(&eval_tree_kernel<L0P, R, A, MINB>);
+    return reinterpret_cast<const void *>(&eval_tree_kernel<L0P, R, A, NT, MINB>);
 }
 
 size_t eval_smem_bytes(const mpx_plan *pl, int R, int NT, int stages)
@@ -420,7 +452,7 @@ size_t eval_smem_bytes(const mpx_plan *pl, int R, int NT, int stages)
     const int U = m > 2 ? m - 2 : 0;
     const int me1 = m >= 2 ? pl->max_exp[1] : 0;
     size_t doubles = (size_t)((m * pl->gp_rows + 1) & ~1) + (size_t)(me1 + 1) * R * NT +
-                     (size_t)3 * U * R * NT;
+                     (size_t)2 * U * R * NT;
     return 128 + (size_t)stages * STAGE_BYTES + doubles * 8;
 }
 
@@ -431,37 +463,47 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
                     cudaStream_t stream)
 {
     if (P == 0) return MPX_OK;
-    const int L0 = pl->max_exp[0] + 1;
-    // kernel variants: (dimension-0 table size, points per thread, min CTAs/SM)
+    const int l0p = mpx_l0p_for(pl->max_exp[0]);
+    // kernel variants: (dimension-0 table size, points per thread, threads per CTA); for each
+    // table size the first entry whose shared memory fits is taken
     static const Variant variants[] = {
-        {10, 4, 256, kfn<10, 4, 1, 1>()},
-        {18, 4, 256, kfn<18, 4, 1, 1>()},
-        {34, 2, 256, kfn<34, 2, 2, 1>()},
-        {66, 1, 256, kfn<66, 1, 2, 1>()},
+        {10, 4, 256, kfn<10, 4, 1, 256, 1>()},
+        {10, 4, 128, kfn<10, 4, 1, 128, 1>()},
+        {10, 4, 64, kfn<10, 4, 1, 64, 1>()},
+        {18, 4, 256, kfn<18, 4, 1, 256, 1>()},
+        {18, 4, 128, kfn<18, 4, 1, 128, 1>()},
+        {18, 4, 64, kfn<18, 4, 1, 64, 1>()},
+        {34, 2, 256, kfn<34, 2, 2, 256, 1>()},
+        {34, 2, 128, kfn<34, 2, 2, 128, 1>()},
+        {34, 2, 64, kfn<34, 2, 2, 64, 1>()},
+        {66, 1, 256, kfn<66, 1, 2, 256, 1>()},
+        {66, 1, 128, kfn<66, 1, 2, 128, 1>()},
+        {66, 1, 64, kfn<66, 1, 2, 64, 1>()},
         // experimental alternatives, selected with MPX_EVAL_VARIANT=<index>
-        {18, 4, 256, kfn<18, 4, 2, 1>()},   // 4: two accumulators per point
-        {18, 2, 256, kfn<18, 2, 2, 2>()},   // 5: 2 points x 2 accumulators, 2 CTAs/SM
-        {18, 3, 256, kfn<18, 3, 1, 1>()},   // 6
+        {18, 4, 256, kfn<18, 4, 2, 256, 1>()},   // 12: two accumulators per point
+        {18, 3, 384, kfn<18, 3, 1, 384, 1>()},   // 13: 3 points, 12 warps
+        {18, 2, 512, kfn<18, 2, 1, 512, 1>()},   // 14: 2 points, 16 warps in one CTA
+        {18, 2, 256, kfn<18, 2, 2, 256, 2>()},   // 15: 2 points x 2 accumulators, 2 CTAs/SM
     };
-    static const int env_variant = getenv("MPX_EVAL_VARIANT") ? atoi(getenv("MPX_EVAL_VARIANT")) : -1;
-    const Variant *v = nullptr;
-    for (const Variant &cand : variants)
-        if (L0 <= cand.l0p) { v = &cand; break; }
-    if (env_variant >= 0 && env_variant < (int)(sizeof(variants) / sizeof(variants[0])) &&
-        L0 <= variants[env_variant].l0p)
-        v = &variants[env_variant];
-    if (!v) return mpx_fail(MPX_ERR_UNSUPPORTED, "dimension-0 exponent too large for the evaluation kernel");
-
+    constexpr int n_standard = 12;
     int smem_max = 0;
     MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
     // tuning knobs for experiments (defaults are what the library ships with)
-    static const int env_nt = getenv("MPX_EVAL_NT") ? atoi(getenv("MPX_EVAL_NT")) : 0;
+    static const int env_variant = getenv("MPX_EVAL_VARIANT") ? atoi(getenv("MPX_EVAL_VARIANT")) : -1;
     static const int env_stages = getenv("MPX_EVAL_STAGES") ? atoi(getenv("MPX_EVAL_STAGES")) : 0;
     int stages = env_stages > 0 ? env_stages : 4;
     if (stages > MPX_STAGES) stages = MPX_STAGES;
     if (stages < 2) stages = 2;
-    int nt = env_nt > 0 ? env_nt : v->nt;
-    while (nt > 32 && eval_smem_bytes(pl, v->r, nt, stages) > (size_t)smem_max) nt >>= 1;
+    const Variant *v = nullptr;
+    for (int i = 0; i < n_standard && !v; ++i)
+        if (variants[i].l0p == l0p &&
+            eval_smem_bytes(pl, variants[i].r, variants[i].nt, stages) <= (size_t)smem_max)
+            v = &variants[i];
+    if (env_variant >= 0 && env_variant < (int)(sizeof(variants) / sizeof(variants[0])) &&
+        variants[env_variant].l0p == l0p)
+        v = &variants[env_variant];
+    if (!v) return mpx_fail(MPX_ERR_UNSUPPORTED, "tables of this index set do not fit shared memory");
+    const int nt = v->nt;
     const size_t smem = eval_smem_bytes(pl, v->r, nt, stages);
     if (smem > (size_t)smem_max)
         return mpx_fail(MPX_ERR_UNSUPPORTED, "tables of this index set do not fit shared memory");

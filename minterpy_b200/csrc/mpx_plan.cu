@@ -57,12 +57,15 @@ int64_t find_sorted(const int64_t *e, const std::vector<int64_t> &order, int m,
 // Evaluation program.  Rows are visited in lexicographic order.  A LEAF is a maximal run
 // of rows with equal exponents in dimensions 1.. and strictly increasing dimension-0
 // exponent; its coefficients occupy slots 0..len-1 (len = largest e0 + 1, holes and the
-// even-length padding get slot_src = -1 => coefficient 0).
+// even-length padding get slot_src = -1 => coefficient 0).  Leaves are grouped into
+// records (format: mpx_common.h); coefficient slots follow the order the kernel walks.
 // ---------------------------------------------------------------------------------------
 int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_t> &order,
-                    EvalProgram &pg, std::string &err)
+                    int l0p, EvalProgram &pg, std::string &err)
 {
     const int U = std::max(m - 2, 0);
+    const int ncw = mpx_count_words(l0p);
+    const int cap_words = MPX_DESC_WORDS - MPX_DESC_HDR;
     struct Leaf { int64_t first, count; int len; };
     std::vector<Leaf> leaves;
     for (int64_t s = 0; s < N;) {
@@ -82,12 +85,28 @@ int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_
     pg.n_leaves = (int64_t)leaves.size();
     pg.fma_per_point = 0;
     pg.other_fp64_per_point = 0;
+    pg.desc.clear();
+    pg.slot_src.clear();
+    pg.n_chunks = 0;
+    pg.slot_src.resize(MPX_COEF_CAP, -1);
 
-    std::vector<uint32_t> words;   // words of the current chunk (records)
+    std::vector<uint32_t> words;   // words of the current chunk
     int coef_used = 0;
-    bool run_open = false;
-    int run_word = 0, run_count = 0, run_lenp = 0, run_e1_next = 0;
+    // the record under construction
+    bool open = false;
+    uint32_t hdr = 0;
+    std::vector<uint32_t> counts(ncw, 0u), ext;
+    int rec_e1_next = 0, rec_last_k = 0;
+
+    auto close_record = [&]() {
+        if (!open) return;
+        words.push_back(hdr);
+        for (uint32_t c : counts) words.push_back(c);
+        for (uint32_t x : ext) words.push_back(x);
+        open = false;
+    };
     auto flush = [&]() {
+        close_record();
         size_t base = pg.desc.size();
         pg.desc.resize(base + MPX_DESC_WORDS, 0u);
         pg.desc[base] = (uint32_t)words.size();
@@ -97,55 +116,59 @@ int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_
         words.clear();
         coef_used = 0;
     };
-    pg.desc.clear();
-    pg.slot_src.clear();
-    pg.n_chunks = 0;
-    pg.slot_src.resize(MPX_COEF_CAP, -1);
 
     for (size_t li = 0; li < leaves.size(); ++li) {
         const Leaf &lf = leaves[li];
         const int64_t *cur = e + order[lf.first] * m;
         const int64_t *nxt = (li + 1 < leaves.size()) ? e + order[leaves[li + 1].first] * m : nullptr;
         const int lenp = (lf.len + 1) & ~1;
+        const int K = lenp / 2;
         const int e1 = (m >= 2) ? (int)cur[1] : 0;
         // highest dimension in which the next leaf differs
         int D = 1;
-        bool last = (nxt == nullptr);
+        const bool last = (nxt == nullptr);
         if (last) {
             D = m - 1;
         } else {
             for (int i = m - 1; i >= 1; --i) if (nxt[i] != cur[i]) { D = i; break; }
         }
-        int nf = last ? U : std::max(D - 1, 0);
-        std::vector<uint32_t> ext;
-        uint32_t w = (uint32_t)(lenp / 2) | ((uint32_t)e1 << 6) | ((uint32_t)nf << 14);
-        if (last) w |= MPX_D_LAST;
+        const int nf = last ? U : std::max(D - 1, 0);
+        uint32_t tail = (uint32_t)nf << 8;          // fold / advance fields of this leaf
+        std::vector<uint32_t> leaf_ext;
+        if (last) tail |= MPX_D_LAST;
         if (nf > 0 && !last) {
             // level u = nf-1 (dimension D) advances from cur[D] to nxt[D]; levels below restart
             int64_t adv = nxt[D] - cur[D];
             bool regular = (adv == 1);
             for (int i = 2; i < D; ++i) regular = regular && (nxt[i] == 0);
             if (regular) {
-                w |= (uint32_t)cur[D] << 19;
+                tail |= (uint32_t)cur[D] << 14;
             } else {
-                w |= MPX_D_IRREG;
-                ext.push_back((uint32_t)cur[D] | ((uint32_t)adv << 8));
-                for (int i = 2; i < D; ++i) ext.push_back((uint32_t)nxt[i]);
+                tail |= MPX_D_IRREG;
+                leaf_ext.push_back((uint32_t)cur[D] | ((uint32_t)adv << 8));
+                for (int i = 2; i < D; ++i) leaf_ext.push_back((uint32_t)nxt[i]);
                 pg.other_fp64_per_point += 2 * (adv - 1);
                 for (int i = 2; i < D; ++i) pg.other_fp64_per_point += 2 * nxt[i];
             }
             pg.other_fp64_per_point += 2;
         }
-        // extend the previous record into a run when this leaf continues it: same padded
-        // length, next dimension-1 exponent, nothing folded in between, same chunk
-        const int cap_words = MPX_DESC_WORDS - MPX_DESC_HDR;
+        // can the leaf join the open record?  next dimension-1 exponent, length not
+        // increasing, nibble not full, and everything still fits into the chunk
         const bool fits_coef = coef_used + lenp <= MPX_COEF_CAP;
-        const bool merged = fits_coef && run_open && lenp == run_lenp && e1 == run_e1_next &&
-                            run_count < 16 && (int)(words.size() + ext.size()) <= cap_words;
-        if (!merged && (!fits_coef || (int)(words.size() + 1 + ext.size()) > cap_words)) {
-            flush();
-            run_open = false;
+        bool join = open && fits_coef && e1 == rec_e1_next && K <= rec_last_k &&
+                    ((counts[(K - 1) / 8] >> (4 * ((K - 1) % 8))) & 15u) < 15u &&
+                    (int)(words.size() + 1 + ncw + leaf_ext.size()) <= cap_words;
+        if (!join) {
+            close_record();
+            if (!fits_coef || (int)(words.size() + 1 + ncw + leaf_ext.size()) > cap_words) flush();
+            open = true;
+            hdr = (uint32_t)e1;
+            std::fill(counts.begin(), counts.end(), 0u);
+            ext.clear();
         }
+        counts[(K - 1) / 8] += 1u << (4 * ((K - 1) % 8));
+        rec_last_k = K;
+        rec_e1_next = e1 + 1;
         // coefficient slots of this leaf
         int32_t *slots = pg.slot_src.data() + (size_t)pg.n_chunks * MPX_COEF_CAP + coef_used;
         for (int64_t r = 0; r < lf.count; ++r) {
@@ -153,23 +176,13 @@ int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_
             slots[e[row * m]] = (int32_t)row;
         }
         coef_used += lenp;
-        if (merged) {
-            uint32_t &rw = words[run_word];
-            rw = (rw & 0x0fffffffu) | ((uint32_t)run_count << 28);   // leaves in the run - 1
-            rw |= w & 0x0fffc000u;        // fold / advance fields come from the run's last leaf
-            run_count++;
-            run_e1_next = e1 + 1;
-        } else {
-            run_word = (int)words.size();
-            words.push_back(w);
-            run_count = 1;
-            run_lenp = lenp;
-            run_e1_next = e1 + 1;
-        }
-        for (uint32_t x : ext) words.push_back(x);
-        // a leaf that folds, advances irregularly or ends the program closes its run
-        run_open = (nf == 0) && !last;
         pg.fma_per_point += lenp + 1 + nf;
+        // a leaf that folds or ends the program closes its record and hands it its tail
+        if (nf > 0 || last) {
+            hdr |= tail;
+            ext = leaf_ext;
+            close_record();
+        }
     }
     flush();
     pg.slot_src.resize((size_t)pg.n_chunks * MPX_COEF_CAP);
@@ -248,7 +261,7 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
     pl->complete = complete;
 
     std::string err;
-    int rc = compile_program(e, N, m, order, pl->prog, err);
+    int rc = compile_program(e, N, m, order, mpx_l0p_for(pl->max_exp[0]), pl->prog, err);
     if (rc != MPX_OK) return mpx_fail(rc, err);
     // upper-level exponents of the first leaf (0 for every downward-closed set)
     for (int i = 2; i < m; ++i) {
@@ -376,7 +389,10 @@ extern "C" int mpx_debug_program(const int64_t *exponents_h, int64_t N, int m, u
     std::stable_sort(order.begin(), order.end(), less);
     EvalProgram pg;
     std::string err;
-    int rc = compile_program(exponents_h, N, m, order, pg, err);
+    int max0 = 0;
+    for (int64_t j = 0; j < N; ++j) max0 = std::max<int>(max0, (int)exponents_h[j * m]);
+    if (max0 > MPX_MAX_L0 - 2) return mpx_fail(MPX_ERR_UNSUPPORTED, "dimension-0 exponent too large");
+    int rc = compile_program(exponents_h, N, m, order, mpx_l0p_for(max0), pg, err);
     if (rc != MPX_OK) return mpx_fail(rc, err);
     if (n_chunks_out) *n_chunks_out = pg.n_chunks;
     if (fma_out) *fma_out = pg.fma_per_point;

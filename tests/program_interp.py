@@ -12,7 +12,7 @@ import numpy as np
 from minterpy_b200 import _lib
 
 DESC_WORDS, DESC_HDR, COEF_CAP = 256, 4, 512
-D_IRREG, D_LAST = 1 << 18, 1 << 27
+D_IRREG, D_LAST = 1 << 12, 1 << 13
 
 
 def compile_program(exponents):
@@ -29,12 +29,19 @@ def compile_program(exponents):
     return desc.reshape(-1, DESC_WORDS), slots.reshape(-1, COEF_CAP), fma.value
 
 
+def l0p_for(max_exp0):
+    L0 = max_exp0 + 1
+    return 10 if L0 <= 10 else 18 if L0 <= 18 else 34 if L0 <= 34 else 66
+
+
 def run_program(desc, slots, x, coeffs, exponents, gp):
     """Value of sum_j coeffs[j] * N_j(x) for ONE point x, walking the program."""
     e = np.asarray(exponents)
     N, m = e.shape
     U = max(m - 2, 0)
     mx = e.max(axis=0)
+    l0p = l0p_for(int(mx[0]))
+    ncw = (l0p // 2 + 7) // 8
     order = np.lexsort(e.T)
     T0 = np.zeros(66)
     T0[0] = 1.0
@@ -60,20 +67,24 @@ def run_program(desc, slots, x, coeffs, exponents, gp):
         end = DESC_HDR + int(dw[0])
         while i < end:
             w = int(dw[i])
-            np_, e1, nf, count = w & 63, (w >> 6) & 255, (w >> 14) & 15, (w >> 28) + 1
-            for j in range(count):           # a run: equal-length leaves, e1 counting upwards
-                a = 0.0
-                for s in range(2 * np_ - 1, -1, -1):
-                    a += packed[cp + s] * T0[s]
+            counts = [int(v) for v in dw[i + 1:i + 1 + ncw]]
+            i += 1 + ncw
+            e1, nf = w & 255, (w >> 8) & 15
+            for K in range(l0p // 2, 0, -1):           # lengths walk downwards
+                cnt = (counts[(K - 1) // 8] >> (4 * ((K - 1) % 8))) & 15
+                for _ in range(cnt):
+                    a = 0.0
+                    for s in range(2 * K - 1, -1, -1):
+                        a += packed[cp + s] * T0[s]
+                        fma += 1
+                    cp += 2 * K
+                    acc1 += T1[e1] * a
+                    e1 += 1
                     fma += 1
-                cp += 2 * np_
-                acc1 += T1[e1 + j] * a
-                fma += 1
             if nf:
-                adv, cur = 1, (w >> 19) & 255
+                adv, cur = 1, (w >> 14) & 255
                 irregular, last = bool(w & D_IRREG), bool(w & D_LAST)
                 if irregular:
-                    i += 1
                     cur, adv = int(dw[i]) & 255, int(dw[i]) >> 8
                 low, acc1 = acc1, 0.0
                 for u in range(nf):
@@ -92,6 +103,5 @@ def run_program(desc, slots, x, coeffs, exponents, gp):
                             for j in range(adv):
                                 t[u] *= xu[u] - gp[cur + j, 2 + u]
                 if irregular:
-                    i += nf - 1
-            i += 1
+                    i += nf
     return (acc[U - 1] if U > 0 else acc1), fma
