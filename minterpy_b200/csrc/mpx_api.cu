@@ -54,8 +54,35 @@ extern "C" int mpx_dds(mpx_plan *pl, double *vals, int k, int64_t ld, void *stre
 }
 
 // ---- host-buffer variants ----------------------------------------------------------------
-// Evaluation: points are processed in blocks; block b+1 is uploaded on one stream while
-// block b is evaluated and block b-1 is downloaded (two device buffers, two streams).
+namespace {
+
+int grow(double **buf, size_t *cap, size_t bytes)
+{
+    if (bytes <= *cap) return MPX_OK;
+    if (*buf) MPX_CUDA(cudaFree(*buf));
+    *buf = nullptr;
+    *cap = 0;
+    MPX_CUDA(cudaMalloc((void **)buf, bytes));
+    *cap = bytes;
+    return MPX_OK;
+}
+
+// row-major (rows x cols) copy between a pitched and a dense buffer; a dense source/target
+// pair degenerates to one linear copy
+cudaError_t copy_rows(void *dst, size_t dst_ld, const void *src, size_t src_ld, size_t cols,
+                      size_t rows, cudaMemcpyKind kind, cudaStream_t st)
+{
+    if (dst_ld == cols && src_ld == cols)
+        return cudaMemcpyAsync(dst, src, rows * cols * 8, kind, st);
+    return cudaMemcpy2DAsync(dst, dst_ld * 8, src, src_ld * 8, cols * 8, rows, kind, st);
+}
+
+}  // namespace
+
+// Evaluation with host buffers.  The coefficients are uploaded and packed once; the points go
+// through two device blocks on two streams, so that the upload of block b+1 and the download
+// of block b-1 overlap the evaluation of block b.  Staging buffers and streams belong to the
+// plan and are reused by later calls.
 extern "C" int mpx_eval_host(mpx_plan *pl, const double *xx_h, int64_t P, int64_t ld_xx,
                              const double *coeffs_h, int k, int64_t ld_c, double *out_h,
                              int64_t ld_out)
@@ -69,71 +96,47 @@ extern "C" int mpx_eval_host(mpx_plan *pl, const double *xx_h, int64_t P, int64_
     if (ld_xx < m || ld_c < k || ld_out < k) return mpx_fail(MPX_ERR_ARG, "leading dimension too small");
     DeviceGuard dg(pl->device);
     if (!dg.ok) return mpx_fail(MPX_ERR_CUDA, "cannot select the plan's CUDA device");
+    std::lock_guard<std::mutex> lock(pl->mu);
 
-    const int64_t block = std::min<int64_t>(P, (int64_t)1 << 22);   // 4 Mi points per block
+    // block size: ~64 MiB of points+values per block, at least 64 Ki points
+    int64_t block = ((int64_t)64 << 20) / (8 * (m + k));
+    block = std::max<int64_t>(block, (int64_t)1 << 16);
+    block = std::min(block, P);
     const int nbuf = (P > block) ? 2 : 1;
-    double *d_c = nullptr, *d_x[2] = {nullptr, nullptr}, *d_o[2] = {nullptr, nullptr};
-    cudaStream_t st[2] = {nullptr, nullptr};
-    int status = MPX_OK;
-    auto cleanup = [&]() {
-        cudaFree(d_c);
-        for (int b = 0; b < 2; ++b) {
-            cudaFree(d_x[b]);
-            cudaFree(d_o[b]);
-            if (st[b]) cudaStreamDestroy(st[b]);
-        }
-    };
-#define MPX_TRY(expr)                                                                          \
-    do {                                                                                       \
-        cudaError_t _e = (expr);                                                               \
-        if (_e != cudaSuccess) {                                                               \
-            status = mpx_fail(MPX_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
-            cleanup();                                                                         \
-            return status;                                                                     \
-        }                                                                                      \
-    } while (0)
-    MPX_TRY(cudaMalloc((void **)&d_c, (size_t)pl->N * k * sizeof(double)));
-    MPX_TRY(cudaMemcpy2D(d_c, (size_t)k * 8, coeffs_h, (size_t)ld_c * 8, (size_t)k * 8, pl->N,
-                         cudaMemcpyHostToDevice));
+    for (int b = 0; b < 2; ++b)
+        if (!pl->h_stream[b]) MPX_CUDA(cudaStreamCreateWithFlags(&pl->h_stream[b], cudaStreamNonBlocking));
+    if (!pl->h_event) MPX_CUDA(cudaEventCreateWithFlags(&pl->h_event, cudaEventDisableTiming));
+    if ((rc = grow(&pl->h_c, &pl->h_c_cap, (size_t)pl->N * k * 8)) != MPX_OK) return rc;
     for (int b = 0; b < nbuf; ++b) {
-        MPX_TRY(cudaMalloc((void **)&d_x[b], (size_t)block * m * sizeof(double)));
-        MPX_TRY(cudaMalloc((void **)&d_o[b], (size_t)block * k * sizeof(double)));
-        MPX_TRY(cudaStreamCreateWithFlags(&st[b], cudaStreamNonBlocking));
+        if ((rc = grow(&pl->h_x[b], &pl->h_x_cap[b], (size_t)block * m * 8)) != MPX_OK) return rc;
+        if ((rc = grow(&pl->h_o[b], &pl->h_o_cap[b], (size_t)block * k * 8)) != MPX_OK) return rc;
     }
-    {
-        // one stream at a time may use the plan's scratch: pack once by evaluating block 0
-        // first; later blocks repack the same coefficients (cheap), serialised by an event
-        std::lock_guard<std::mutex> lock(pl->mu);
-        cudaEvent_t ev_prev = nullptr;
-        int64_t nblk = (P + block - 1) / block;
-        for (int64_t b = 0; b < nblk && status == MPX_OK; ++b) {
-            const int s = (int)(b % nbuf);
-            const int64_t p0 = b * block, np = std::min(block, P - p0);
-            cudaError_t e = cudaMemcpy2DAsync(d_x[s], (size_t)m * 8, xx_h + p0 * ld_xx,
-                                              (size_t)ld_xx * 8, (size_t)m * 8, np,
-                                              cudaMemcpyHostToDevice, st[s]);
-            if (e == cudaSuccess && ev_prev) e = cudaStreamWaitEvent(st[s], ev_prev, 0);
-            if (e != cudaSuccess) { status = mpx_fail(MPX_ERR_CUDA, cudaGetErrorString(e)); break; }
-            status = mpx_launch_eval(pl, d_x[s], np, m, d_c, k, k, d_o[s], k, st[s]);
-            if (status != MPX_OK) break;
-            if (ev_prev) cudaEventDestroy(ev_prev);
-            ev_prev = nullptr;
-            e = cudaEventCreateWithFlags(&ev_prev, cudaEventDisableTiming);
-            if (e == cudaSuccess) e = cudaEventRecord(ev_prev, st[s]);
-            if (e == cudaSuccess)
-                e = cudaMemcpy2DAsync(out_h + p0 * ld_out, (size_t)ld_out * 8, d_o[s], (size_t)k * 8,
-                                      (size_t)k * 8, np, cudaMemcpyDeviceToHost, st[s]);
-            if (e != cudaSuccess) { status = mpx_fail(MPX_ERR_CUDA, cudaGetErrorString(e)); break; }
-        }
-        if (ev_prev) cudaEventDestroy(ev_prev);
-        for (int b = 0; b < nbuf; ++b) {
-            cudaError_t e = cudaStreamSynchronize(st[b]);
-            if (e != cudaSuccess && status == MPX_OK) status = mpx_fail(MPX_ERR_CUDA, cudaGetErrorString(e));
-        }
+
+    cudaStream_t s0 = pl->h_stream[0];
+    MPX_CUDA(copy_rows(pl->h_c, k, coeffs_h, ld_c, k, pl->N, cudaMemcpyHostToDevice, s0));
+    if ((rc = mpx_launch_eval(pl, nullptr, 0, m, pl->h_c, k, k, nullptr, k, s0)) != MPX_OK) return rc;
+    MPX_CUDA(cudaEventRecord(pl->h_event, s0));
+    MPX_CUDA(cudaStreamWaitEvent(pl->h_stream[1], pl->h_event, 0));
+
+    int status = MPX_OK;
+    const int64_t nblk = (P + block - 1) / block;
+    for (int64_t b = 0; b < nblk && status == MPX_OK; ++b) {
+        const int s = (int)(b % nbuf);
+        cudaStream_t st = pl->h_stream[s];
+        const int64_t p0 = b * block, np = std::min(block, P - p0);
+        cudaError_t e = copy_rows(pl->h_x[s], m, xx_h + p0 * ld_xx, ld_xx, m, np,
+                                  cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) { status = mpx_fail(MPX_ERR_CUDA, cudaGetErrorString(e)); break; }
+        status = mpx_launch_eval(pl, pl->h_x[s], np, m, nullptr, k, k, pl->h_o[s], k, st);
+        if (status != MPX_OK) break;
+        e = copy_rows(out_h + p0 * ld_out, ld_out, pl->h_o[s], k, k, np, cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) { status = mpx_fail(MPX_ERR_CUDA, cudaGetErrorString(e)); break; }
     }
-    cleanup();
+    for (int b = 0; b < 2; ++b) {
+        cudaError_t e = cudaStreamSynchronize(pl->h_stream[b]);
+        if (e != cudaSuccess && status == MPX_OK) status = mpx_fail(MPX_ERR_CUDA, cudaGetErrorString(e));
+    }
     return status;
-#undef MPX_TRY
 }
 
 extern "C" int mpx_dds_host(mpx_plan *pl, const double *in_h, int k, int64_t ld_in, double *out_h,

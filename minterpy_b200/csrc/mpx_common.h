@@ -80,6 +80,11 @@ struct mpx_plan {
     std::mutex mu;
     double *d_scratch = nullptr;
     size_t scratch_bytes = 0;
+    // staging for the host-buffer entry points: two streams, two point/value blocks
+    cudaStream_t h_stream[2] = {nullptr, nullptr};
+    cudaEvent_t h_event = nullptr;
+    double *h_x[2] = {nullptr, nullptr}, *h_o[2] = {nullptr, nullptr}, *h_c = nullptr;
+    size_t h_x_cap[2] = {0, 0}, h_o_cap[2] = {0, 0}, h_c_cap = 0;   // bytes
 };
 
 // error plumbing --------------------------------------------------------------------------

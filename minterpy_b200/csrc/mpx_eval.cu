@@ -458,11 +458,13 @@ size_t eval_smem_bytes(const mpx_plan *pl, int R, int NT, int stages)
 
 }  // namespace
 
+// coefficients == nullptr: the plan's scratch already holds the packed image of these k
+// polynomials (mpx_eval_host packs once, then evaluates block after block)
 int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
                     const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                     cudaStream_t stream)
 {
-    if (P == 0) return MPX_OK;
+    if (P == 0 && coeffs == nullptr) return MPX_OK;
     const int l0p = mpx_l0p_for(pl->max_exp[0]);
     // kernel variants: (dimension-0 table size, points per thread, threads per CTA); for each
     // table size the first entry whose shared memory fits is taken
@@ -510,15 +512,16 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
 
     // pack the coefficients into the program image (plan scratch)
     const int64_t n_slots = (int64_t)pl->prog.n_chunks * MPX_COEF_CAP;
-    int rc = mpx_ensure_scratch(pl, (size_t)n_slots * k * sizeof(double));
-    if (rc != MPX_OK) return rc;
-    {
+    if (coeffs) {
+        int rc = mpx_ensure_scratch(pl, (size_t)n_slots * k * sizeof(double));
+        if (rc != MPX_OK) return rc;
         const int64_t total = n_slots * k;
         const int tb = 256;
         pack_coeffs_kernel<<<(unsigned)((total + tb - 1) / tb), tb, 0, stream>>>(
             coeffs, ld_c, k, pl->d_slot_src, n_slots, pl->d_scratch);
         MPX_CUDA(cudaGetLastError());
     }
+    if (P == 0) return MPX_OK;
 
     EvalParams prm;
     prm.xx = xx; prm.ld_xx = ld_xx; prm.P = P; prm.out = out; prm.ld_out = ld_out;

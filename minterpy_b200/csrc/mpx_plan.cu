@@ -336,6 +336,13 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
     cudaFree(pl->d_exp8);
     cudaFree(pl->d_max_exp);
     cudaFree(pl->d_scratch);
+    for (int b = 0; b < 2; ++b) {
+        cudaFree(pl->h_x[b]);
+        cudaFree(pl->h_o[b]);
+        if (pl->h_stream[b]) cudaStreamDestroy(pl->h_stream[b]);
+    }
+    cudaFree(pl->h_c);
+    if (pl->h_event) cudaEventDestroy(pl->h_event);
     for (DdsDim &dd : pl->dds) {
         cudaFree(dd.d_off);
         cudaFree(dd.d_rows);

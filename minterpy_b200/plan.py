@@ -27,6 +27,17 @@ def _current_device():
     return torch.cuda.current_device()
 
 
+def _host_result(shape):
+    """Result array for the NumPy path, backed by page-locked memory from torch's caching host
+    allocator (a device-to-host copy into pageable memory is several times slower, and the
+    allocator recycles the block once the array is garbage collected)."""
+    n = int(np.prod(shape))
+    if n * 8 < (1 << 20):
+        return np.empty(shape, dtype=np.float64)
+    import torch
+    return torch.empty(shape, dtype=torch.float64, pin_memory=True).numpy()
+
+
 class Plan:
     def __init__(self, exponents, generating_points, device=None):
         e = np.ascontiguousarray(exponents, dtype=np.int64)
@@ -72,7 +83,7 @@ class Plan:
         xx = np.ascontiguousarray(xx, dtype=np.float64)
         coeffs = np.ascontiguousarray(coeffs, dtype=np.float64)
         P, k = xx.shape[0], coeffs.shape[1]
-        out = np.empty((P, k), dtype=np.float64)
+        out = _host_result((P, k))
         if P:
             rc = _lib.lib().mpx_eval_host(self._h, xx.ctypes.data, P, self.m, coeffs.ctypes.data,
                                           k, k, out.ctypes.data, k)
