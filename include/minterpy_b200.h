@@ -89,6 +89,29 @@ int mpx_eval(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
              const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
              void *stream);
 
+/*
+ * mpx_eval for callers that must not allocate device memory.  (No counterpart in the
+ * reference: the reference has no device memory at all.)
+ * Meant for a host program that gave all device memory to its own pool at start-up, where a
+ * later cudaMalloc fails, or that cannot take the device-wide synchronisation of
+ * cudaMalloc / cudaFree inside its evaluation loop.  Same arguments and results as mpx_eval,
+ * but the packed coefficients go to a fixed 8 MiB array inside the library's device image
+ * (held by every GPU that loads the library, until exit) instead of plan scratch that may
+ * have to grow; the call allocates and frees nothing.
+ *   - limit: chunks * 512 * k * 8 bytes <= 8 MiB (chunks = MPX_INFO_CHUNKS; 39 polynomials per
+ *     call at BASELINE config 2); beyond that the call returns MPX_ERR_UNSUPPORTED and does
+ *     nothing -- split k, or use mpx_eval.
+ *   - the first call on a device looks the array's address up (set-up); make that first call
+ *     before starting any stream capture.
+ *   - the array is shared by all plans and calls on the device and keeps the last call's
+ *     contents; each call rewrites every slot it reads, so nothing needs clearing, but two
+ *     calls whose kernels overlap on the GPU overwrite each other's coefficients: serialise
+ *     them.
+ */
+int mpx_eval_noalloc(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+                     const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
+                     void *stream);
+
 /* Same, host buffers in and out (pinned or pageable): H2D, kernels and D2H are pipelined
  * over blocks of points.  This is what the NumPy path of the Python mirror calls. */
 int mpx_eval_host(mpx_plan *plan, const double *xx_h, int64_t P, int64_t ld_xx,

@@ -21,6 +21,7 @@ SIGNATURES = {
     "mpx_plan_destroy": (None, [c_vp]),
     "mpx_plan_info": (c_int, [c_vp, c_int, ctypes.POINTER(c_i64)]),
     "mpx_eval": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_int, c_i64, c_vp, c_i64, c_vp]),
+    "mpx_eval_noalloc": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_int, c_i64, c_vp, c_i64, c_vp]),
     "mpx_eval_host": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_int, c_i64, c_vp, c_i64]),
     "mpx_monomials": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_i64, c_int, c_vp]),
     "mpx_dds": (c_int, [c_vp, c_vp, c_int, c_i64, c_vp]),
