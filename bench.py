@@ -304,21 +304,35 @@ def main():
     if rank == 0:
         fma = plan.info(_lib.INFO_EVAL_FMA)
         other = plan.info(_lib.INFO_EVAL_OTHER_FP64)
-        executed = (2 * fma + other) * k          # FP64 flops per point actually issued
         model = model_flops_per_point(e, k)
-        algo = min(model, executed)
         peak_dfma, peak_dmma = measured_fp64_peak()
-        peak = peak_dfma or NOMINAL_FP64_TFLOPS
+        tensor_path = k >= 8 and m <= 8          # mpx_eval_mma.cu (DMMA), else the tree kernel
+        if tensor_path:
+            # per point: every monomial (padded to 32) is formed with m-1 DMUL and contracted
+            # against k (padded to the CTA tile) coefficients on the tensor cores
+            n_pad = -(-N // 32) * 32
+            tile = 8 if k <= 8 else 16 if k <= 16 else 32 if k <= 32 else 64
+            k_pad = -(-k // tile) * tile
+            executed = n_pad * (2 * k_pad + (m - 1)) + 2 * int(e.max(axis=0).sum())
+            fma = n_pad * k_pad
+            peak = peak_dmma or NOMINAL_FP64_TFLOPS
+        else:
+            executed = (2 * fma + other) * k          # FP64 flops per point actually issued
+            fma = fma * k
+            peak = peak_dfma or NOMINAL_FP64_TFLOPS
+        algo = min(model, executed)
         kernel_ms = float(np.median(step_ms))
         achieved = algo * P / (kernel_ms * 1e-3) / 1e12
-        roofline = {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                    "frac": achieved / peak, "traffic": None,
-                    "peak_source": ("measured DFMA rate, tools/fp64_peak.cu on this GPU"
+        roofline = {"bound": "tensor" if tensor_path else "fp64", "achieved": achieved,
+                    "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                    "peak_source": (("measured DMMA (mma.sync f64) rate" if tensor_path else
+                                     "measured DFMA rate") + ", tools/fp64_peak.cu on this GPU"
                                     if peak_dfma else "nominal (fp64_peak tool missing)"),
                     "nominal_peak": NOMINAL_FP64_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP64_TFLOPS,
                     "measured_dmma_peak": peak_dmma,
                     "flops_per_point_model": model, "flops_per_point_executed": executed,
-                    "fma_per_point": fma * k, "kernel": "eval_tree_kernel",
+                    "fma_per_point": fma,
+                    "kernel": "eval_mma_kernel" if tensor_path else "eval_tree_kernel",
                     "kernel_ms": kernel_ms,
                     "hbm_gbs": P * 8 * (m + k) / (kernel_ms * 1e-3) / 1e9}
         cpu = None if args.no_cpu else cpu_baseline(e, gp, k)

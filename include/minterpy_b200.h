@@ -98,8 +98,10 @@ int mpx_eval(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
  * but the packed coefficients go to a fixed 8 MiB array inside the library's device image
  * (held by every GPU that loads the library, until exit) instead of plan scratch that may
  * have to grow; the call allocates and frees nothing.
- *   - limit: chunks * 512 * k * 8 bytes <= 8 MiB (chunks = MPX_INFO_CHUNKS; 39 polynomials per
- *     call at BASELINE config 2); beyond that the call returns MPX_ERR_UNSUPPORTED and does
+ *   - limit: the packed coefficients of one call must fit 8 MiB.  They take
+ *     chunks * 512 * k * 8 bytes for k < 8 (chunks = MPX_INFO_CHUNKS) and about 1.1 * N * k * 8
+ *     bytes (k rounded up to 8, 16, 32 or a multiple of 64) for k >= 8: up to 32 polynomials per
+ *     call at BASELINE config 2.  Beyond that the call returns MPX_ERR_UNSUPPORTED and does
  *     nothing -- split k, or use mpx_eval.
  *   - the first call on a device looks the array's address up (set-up); make that first call
  *     before starting any stream capture.

@@ -73,6 +73,8 @@ struct mpx_plan {
     double *d_gp = nullptr;          // (m x gp_rows) dimension-major copy of the generating points
     uint8_t *d_exp8 = nullptr;       // (N x m) exponents as bytes, for the monomial kernel
     int *d_max_exp = nullptr;        // (m) largest exponent per dimension
+    uint64_t *d_exp64 = nullptr;     // exponents packed 8 bytes per monomial, padded to 32 rows (m <= 8)
+    int mma_chunks = 0;              // ceil(N / 32)
     // dds
     std::vector<DdsDim> dds;         // one per dimension (only if complete)
     int64_t dds_updates = 0;
@@ -113,3 +115,11 @@ int mpx_launch_monomials(mpx_plan *plan, const double *xx, int64_t P, int64_t ld
                          double *out, int64_t ld_out, int triangular, cudaStream_t stream);
 int mpx_launch_dds(mpx_plan *plan, double *vals, int k, int64_t ld, cudaStream_t stream);
 int mpx_ensure_scratch(mpx_plan *plan, size_t bytes);
+// tensor-core (many polynomials) evaluation path, mpx_eval_mma.cu
+bool mpx_mma_eligible(const mpx_plan *plan, int k);
+size_t mpx_mma_scratch_bytes(const mpx_plan *plan, int k);
+int mpx_launch_eval_mma(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+                        const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
+                        cudaStream_t stream);
+// bytes of plan scratch an evaluation of k polynomials needs (either path)
+size_t mpx_eval_scratch_bytes(const mpx_plan *plan, int k);

@@ -19,64 +19,9 @@
 #include <cstdlib>
 
 #include "mpx_common.h"
+#include "mpx_ptx.h"
 
 namespace {
-
-__device__ __forceinline__ uint32_t smem_u32(const void *p)
-{
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n\t"
-        ".reg .pred P1;\n\t"
-        "LAB_WAIT:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-        "@P1 bra DONE;\n\t"
-        "bra LAB_WAIT;\n\t"
-        "DONE:\n\t"
-        "}" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-__device__ __forceinline__ bool mbar_test(uint64_t *bar, uint32_t parity)
-{
-    uint32_t ok;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred P1;\n\t"
-        "mbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, P1;\n\t"
-        "}"
-        : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-    return ok != 0;
-}
-// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
-{
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-            smem_u32(dst)),
-        "l"(src), "r"(bytes), "r"(smem_u32(bar))
-        : "memory");
-}
 
 struct EvalParams {
     const double *xx;
@@ -465,6 +410,8 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
                     cudaStream_t stream)
 {
     if (P == 0 && coeffs == nullptr) return MPX_OK;
+    if (mpx_mma_eligible(pl, k))
+        return mpx_launch_eval_mma(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
     const int l0p = mpx_l0p_for(pl->max_exp[0]);
     // kernel variants: (dimension-0 table size, points per thread, threads per CTA); for each
     // table size the first entry whose shared memory fits is taken
@@ -538,4 +485,10 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
     void *args[] = {(void *)&prm};
     MPX_CUDA(cudaLaunchKernel(v->fn, grid, dim3(nt, 1, 1), args, smem, stream));
     return MPX_OK;
+}
+
+size_t mpx_eval_scratch_bytes(const mpx_plan *pl, int k)
+{
+    if (mpx_mma_eligible(pl, k)) return mpx_mma_scratch_bytes(pl, k);
+    return (size_t)pl->prog.n_chunks * MPX_COEF_CAP * (size_t)k * sizeof(double);
 }

@@ -8,9 +8,9 @@
 // library's device image instead, so the call itself allocates nothing.
 //
 // Cost and limits: every GPU that loads libminterpy_b200.so holds MPX_NOALLOC_BYTES (8 MiB)
-// for the array until the process exits.  A call needs chunks * 512 * k doubles (chunks =
-// MPX_INFO_CHUNKS of the plan) and is refused with MPX_ERR_UNSUPPORTED if that exceeds the
-// array.  All plans and all calls on a device share the one array: it still holds the previous
+// for the array until the process exits.  A call with k < 8 polynomials needs chunks * 512 * k
+// doubles (chunks = MPX_INFO_CHUNKS of the plan), one with more about 1.06 * N * k doubles; it
+// is refused with MPX_ERR_UNSUPPORTED if that exceeds the array.  All plans and all calls on a device share the one array: it still holds the previous
 // call's image when the next call starts (every slot the next call reads is rewritten first,
 // padding included, so nothing has to be cleared), and two calls whose kernels overlap on the
 // GPU -- different streams, different host threads -- would overwrite each other's
@@ -60,11 +60,11 @@ extern "C" int mpx_eval_noalloc(mpx_plan *pl, const double *xx, int64_t P, int64
     if (P == 0) return MPX_OK;
     if (!xx || !coeffs || !out) return mpx_fail(MPX_ERR_ARG, "null device pointer");
     if (ld_xx < pl->m || ld_c < k || ld_out < k) return mpx_fail(MPX_ERR_ARG, "leading dimension too small");
-    const size_t need = (size_t)pl->prog.n_chunks * MPX_COEF_CAP * (size_t)k;
-    if (need > MPX_NOALLOC_SLOTS)
+    const size_t need = mpx_eval_scratch_bytes(pl, k);     // bytes
+    if (need > MPX_NOALLOC_BYTES)
         return mpx_fail(MPX_ERR_UNSUPPORTED,
                         "mpx_eval_noalloc: the packed coefficients of this call need " +
-                            std::to_string(need * sizeof(double)) + " bytes, the fixed scratch holds " +
+                            std::to_string(need) + " bytes, the fixed scratch holds " +
                             std::to_string(MPX_NOALLOC_BYTES) + "; use fewer polynomials per call or mpx_eval");
     DeviceGuard dg(pl->device);
     if (!dg.ok) return mpx_fail(MPX_ERR_CUDA, "cannot select the plan's CUDA device");
@@ -73,7 +73,7 @@ extern "C" int mpx_eval_noalloc(mpx_plan *pl, const double *xx, int64_t P, int64
     if (rc != MPX_OK) return rc;
 
     // Run the regular launch sequence with the fixed array standing in for the plan's scratch.
-    // Its capacity check passes (need <= MPX_NOALLOC_SLOTS), so nothing is allocated or freed.
+    // Its capacity check passes (need <= MPX_NOALLOC_BYTES), so nothing is allocated or freed.
     std::lock_guard<std::mutex> lock(pl->mu);
     double *saved_ptr = pl->d_scratch;
     const size_t saved_bytes = pl->scratch_bytes;

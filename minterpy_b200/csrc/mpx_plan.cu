@@ -283,6 +283,13 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
     std::vector<uint8_t> e8((size_t)N * m);
     for (size_t t = 0; t < e8.size(); ++t) e8[t] = (uint8_t)e[t];
     if ((rc = upload(&pl->d_exp8, e8)) != MPX_OK) return rc;
+    if (m <= 8) {
+        pl->mma_chunks = (int)((N + 31) / 32);
+        std::vector<uint64_t> e64((size_t)pl->mma_chunks * 32, 0ull);
+        for (int64_t j = 0; j < N; ++j)
+            for (int i = 0; i < m; ++i) e64[j] |= (uint64_t)e[j * m + i] << (8 * i);
+        if ((rc = upload(&pl->d_exp64, e64)) != MPX_OK) return rc;
+    }
     std::vector<int> mxv(pl->max_exp, pl->max_exp + m);
     if ((rc = upload(&pl->d_max_exp, mxv)) != MPX_OK) return rc;
 
@@ -335,6 +342,7 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
     cudaFree(pl->d_gp);
     cudaFree(pl->d_exp8);
     cudaFree(pl->d_max_exp);
+    cudaFree(pl->d_exp64);
     cudaFree(pl->d_scratch);
     for (int b = 0; b < 2; ++b) {
         cudaFree(pl->h_x[b]);

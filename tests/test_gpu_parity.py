@@ -265,3 +265,31 @@ def test_dense_apply(mpb):
                                         out.data_ptr(), k, None)
         _lib.check(rc)
         assert rel_err(out.cpu().numpy(), T @ c) <= 1e-13
+
+
+@pytest.mark.parametrize("k", [8, 9, 16, 31, 64, 100])
+def test_many_polynomials_tensor_core_path(mpb, golden_cfg, k):
+    """k >= 8 takes the DMMA kernel (csrc/mpx_eval_mma.cu); same tolerance as the tree kernel."""
+    for tag, npts in (("cfg3", 333), ("cfg2", 97)):
+        g = golden_cfg(tag)
+        e, gp = g["exponents"], g["generating_points"]
+        rng = np.random.default_rng(k)
+        c = rng.uniform(-1, 1, (e.shape[0], k))
+        xx = rng.uniform(-1, 1, (npts, e.shape[1]))
+        got = mpb.get_plan(e, gp).eval(xx, c)
+        ref = oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=4)
+        assert rel_err(got, ref) <= EVAL_RTOL
+
+
+def test_tensor_core_path_irregular_and_small(mpb):
+    rng = np.random.default_rng(21)
+    for trial in range(6):
+        m = int(rng.integers(1, 8))
+        e = np.unique(rng.integers(0, 7, (int(rng.integers(1, 150)), m)), axis=0).astype(np.int64)
+        rng.shuffle(e)
+        gp = rng.uniform(-1, 1, (8, m))
+        k = int(rng.integers(8, 40))
+        c = rng.uniform(-1, 1, (e.shape[0], k))
+        xx = rng.uniform(-1, 1, (int(rng.integers(1, 300)), m))
+        got = mpb.Plan(e, gp).eval(xx, c)
+        assert rel_err(got, oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL

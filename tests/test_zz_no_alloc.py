@@ -39,8 +39,8 @@ def test_noalloc_matches_eval_twice_in_a_row():
     N, m = e.shape
     plan = mpb.Plan(e, gp)
     gen = torch.Generator(device="cuda").manual_seed(99)
-    # two calls with different coefficients, polynomial counts and point counts
-    for P, k in ((5000, 3), (1777, 1)):
+    # calls in a row with different coefficients, polynomial counts and point counts
+    for P, k in ((5000, 3), (1777, 1), (3001, 20)):     # k = 20 takes the tensor-core path
         xx = torch.rand((P, m), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
         c = torch.rand((N, k), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
         rc, ref = _call(lib.mpx_eval, plan, xx, c)
@@ -63,8 +63,7 @@ def test_noalloc_rejects_oversized_request():
     g = golden_io.load("cfg2")
     e, gp = g["exponents"], g["generating_points"]
     plan = mpb.Plan(e, gp)
-    chunks = plan.info(_lib.INFO_CHUNKS)
-    k = (1 << 20) // (chunks * 512) + 1                 # one polynomial too many for 8 MiB
+    k = 64                              # 24 809 x 64 packed coefficients: 13.5 MB > 8 MiB
     xx = torch.zeros((4, e.shape[1]), dtype=torch.float64, device="cuda")
     c = torch.zeros((e.shape[0], k), dtype=torch.float64, device="cuda")
     rc, out = _call(lib.mpx_eval_noalloc, plan, xx, c)
@@ -72,5 +71,5 @@ def test_noalloc_rejects_oversized_request():
     assert "fixed scratch" in _lib.last_error()
     torch.cuda.synchronize()
     assert torch.isnan(out).all()                        # nothing was launched
-    rc, _ = _call(lib.mpx_eval_noalloc, plan, xx, c[:, :k - 1].contiguous())
+    rc, _ = _call(lib.mpx_eval_noalloc, plan, xx, c[:, :32].contiguous())    # 7.2 MB: fits
     assert rc == _lib.MPX_OK
