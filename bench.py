@@ -197,6 +197,7 @@ def main():
     import torch.distributed as dist
     import minterpy_b200 as mpb
     from minterpy_b200 import _lib
+    from minterpy_b200 import distributed as mpd
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -225,7 +226,7 @@ def main():
     if world > 1:
         if rank != 0:
             coeffs.zero_()
-        dist.broadcast(coeffs, src=0)
+        mpd.broadcast_parameters([coeffs], src=0)
     out = torch.empty((P, k), dtype=torch.float64, device=dev)
 
     def step():
@@ -290,15 +291,15 @@ def main():
 
     gather_ms = None
     if world > 1:
-        full = torch.empty((world * P, k), dtype=torch.float64, device=dev)
-        dist.all_gather_into_tensor(full, out)
+        full = mpd.gather_values(out, world * P)          # NCCL all_gather of the result shards
         barrier()
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         g0.record()
-        dist.all_gather_into_tensor(full, out)
+        full = mpd.gather_values(out, world * P)
         g1.record()
         barrier()
         gather_ms = g0.elapsed_time(g1)
+        assert full.shape[0] == world * P
         del full
 
     if rank == 0:
