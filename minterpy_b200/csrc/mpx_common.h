@@ -19,6 +19,9 @@ constexpr int MPX_COEF_CAP = 512;     // coefficient slots (doubles) per chunk a
 constexpr int MPX_STAGES = 8;         // shared-memory ring depth of the chunk stream
 constexpr int MPX_MAX_L0 = 66;        // dimension-0 table entries a thread can hold in registers
 constexpr int MPX_MAX_M = 16;
+constexpr int MPX_DDS_COLS = 32;      // value columns per CTA of the fused dds kernel
+constexpr int MPX_DDS_MERGE_ROWS = 112; // small slices are merged until a CTA owns this many rows
+constexpr int MPX_DDS_MAX_ROWS = 736; // rows of a slice that fit shared memory (x 32 columns x 8 B)
 
 // Record = one header word, MPX count words, then extension words when MPX_D_IRREG is set.
 // A record covers consecutive leaves (dimension-1 exponent counting upwards from e1_first)
@@ -58,6 +61,29 @@ struct DdsDim {
     double *d_diff = nullptr;   // (L x L) table: diff[l*L + r] = gp[r,d] - gp[l,d], L = max_len
 };
 
+// A group of consecutive dimensions [lo, hi] that the divided-difference kernel handles in
+// one pass: the index set falls apart into SLICES (rows that agree in every dimension outside
+// the group); a slice is loaded into shared memory, all fibers of dimensions hi..lo inside it
+// are processed there, and it is written back.
+struct DdsGroupDim {
+    int dim = 0;
+    int L = 0;                      // longest fiber (side of the diff table)
+    int max_fibers = 0;             // most fibers of this dimension in one slice
+    int32_t *d_slice_fib0 = nullptr;  // n_slices + 1: first fiber of every slice
+    int32_t *d_fib_off = nullptr;     // n_fibers + 1: offsets into d_fib_rows
+    uint16_t *d_fib_rows = nullptr;   // N: slice-local row of every fiber element, e_d ascending
+    double *d_diff = nullptr;         // (L x L): diff[l*L + r] = gp[r,dim] - gp[l,dim]
+    double *d_recip = nullptr;        // (L x L): 1.0 / diff, correctly rounded (host division)
+};
+struct DdsGroup {
+    int lo = 0, hi = 0;
+    int n_slices = 0;
+    int max_rows = 0;               // largest slice
+    int32_t *d_slice_off = nullptr; // n_slices + 1
+    int32_t *d_slice_rows = nullptr;// N: global row of every slice element
+    std::vector<DdsGroupDim> dims;  // hi first
+};
+
 struct mpx_plan {
     int device = 0;
     int64_t N = 0;
@@ -77,6 +103,8 @@ struct mpx_plan {
     int mma_chunks = 0;              // ceil(N / 32)
     // dds
     std::vector<DdsDim> dds;         // one per dimension (only if complete)
+    std::vector<DdsGroup> dds_groups; // fused passes, top dimensions first (only if complete)
+    bool dds_fast_div = true;         // every divisor qualifies for the reciprocal + correction division
     int64_t dds_updates = 0;
     // growable scratch (packed coefficients of the current evaluation call)
     std::mutex mu;

@@ -9,6 +9,8 @@
 // bit-identical: true division, no FMA contraction possible in (a-b)/c.
 // One thread owns one (fiber, column) pair and keeps the fiber in registers; the k value
 // columns are the fastest thread index, so global accesses are coalesced along a row.
+#include <cstdlib>
+
 #include "mpx_common.h"
 
 namespace {
@@ -76,14 +78,171 @@ dds_pass_generic_kernel(double *__restrict__ vals, int64_t ld, int k,
     }
 }
 
+
+// ---- fused kernel: one CTA = one slice x 32 value columns -------------------------------
+// The slice (rows that agree outside the dimension group) is gathered into shared memory as
+// v[row][column]; then, for d = hi .. lo, every fiber of dimension d inside the slice gets the
+// 1-D scheme, one warp per fiber, lane = column:
+//   for i = 1..len-1: for r = i..len-1: v[r] = (v[r] - v[i-1]) / (g[r] - g[i-1]).
+//
+// Division.  Every divisor comes from a small table, so its correctly rounded reciprocal
+// y = RN(1/d) is tabulated too (host division) and the quotient is formed as
+//   q = a*y;  r = fma(-d, q, a);  q' = fma(r, y, q)
+// -- Markstein's correction step, which returns the IEEE quotient RN(a/d) when y is the
+// correctly rounded reciprocal, d's significand is not all ones and nothing over/underflows.
+// The plan tabulates reciprocal 0 for divisors that do not qualify; the kernel falls back to
+// __ddiv_rn for those and for numerators outside [2^-900, 2^900] (zero, subnormal, huge, inf,
+// nan).  tools/div_check.cu
+// compares the sequence with __ddiv_rn on 1e10 random and near-midpoint cases: no mismatch.
+struct DdsDimArgs {
+    const int32_t *slice_fib0;
+    const int32_t *fib_off;
+    const uint16_t *fib_rows;
+    const double *diff;
+    const double *recip;
+    int L;
+};
+struct DdsGroupArgs {
+    const int32_t *slice_off;
+    const int32_t *slice_rows;
+    int n_dims;
+    int max_rows;
+    int max_fibers[MPX_MAX_M];
+    DdsDimArgs dim[MPX_MAX_M];
+};
+
+constexpr int DDS_WARPS = 8;
+constexpr int DDS_MAX_FIBER = 256;
+
+// out of line on purpose: inlined, the compiler evaluates the whole division speculatively
+// next to the fast sequence
+__device__ __noinline__ double dds_true_division(double a, double d) { return __ddiv_rn(a, d); }
+
+template <bool FAST>
+__device__ __forceinline__ double dds_update(double x, double pv, double d, double y)
+{
+    const double a = __dsub_rn(x, pv);
+    if constexpr (FAST) {
+        const double q = __dmul_rn(a, y);
+        const double r = __fma_rn(-d, q, a);
+        const double q2 = __fma_rn(r, y, q);
+        const unsigned ex = ((unsigned)__double2hiint(a) >> 20) & 0x7ffu;
+        // 2^-900 <= |a| < 2^900 and the divisor qualified (its tabulated reciprocal is not 0)
+        if (ex - 123u < 1800u && __double2hiint(y) != 0) return q2;
+        return dds_true_division(a, d);
+    } else {
+        return __ddiv_rn(a, d);
+    }
+}
+
+template <bool FAST>
+__global__ void __launch_bounds__(DDS_WARPS * 32)
+dds_group_kernel(double *__restrict__ vals, int64_t ld, int k, const DdsGroupArgs g)
+{
+    // shared memory: v[max_rows][32] | per dim: diff (L*L), recip (L*L) | per dim: fiber
+    // offsets (max_fibers + 1) and fiber rows as byte offsets into v (max_rows), both u32
+    extern __shared__ __align__(16) unsigned char dsm[];
+    double *v = reinterpret_cast<double *>(dsm);
+    double *stab = v + (size_t)g.max_rows * MPX_DDS_COLS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int s = blockIdx.x;
+    const int col = blockIdx.y * MPX_DDS_COLS + lane;
+    const bool active = col < k;
+    const int r0 = g.slice_off[s];
+    const int nrows = g.slice_off[s + 1] - r0;
+    size_t toff = 0;
+    for (int t = 0; t < g.n_dims; ++t) {
+        const int LL = g.dim[t].L * g.dim[t].L;
+        for (int i = threadIdx.x; i < LL; i += blockDim.x) {
+            stab[toff + i] = g.dim[t].diff[i];
+            stab[toff + LL + i] = g.dim[t].recip[i];
+        }
+        toff += 2 * LL;
+    }
+    uint32_t *meta = reinterpret_cast<uint32_t *>(stab + toff);
+    {
+        // fiber tables of this slice: the sweeps below then touch shared memory only
+        uint32_t *mp = meta;
+        for (int t = 0; t < g.n_dims; ++t) {
+            const DdsDimArgs &gd = g.dim[t];
+            const int f0 = gd.slice_fib0[s], nf = gd.slice_fib0[s + 1] - f0;
+            const int o0 = gd.fib_off[f0];
+            for (int i = threadIdx.x; i <= nf; i += blockDim.x) mp[i] = (uint32_t)(gd.fib_off[f0 + i] - o0);
+            uint32_t *rows = mp + g.max_fibers[t] + 1;
+            for (int i = threadIdx.x; i < nrows; i += blockDim.x)
+                rows[i] = (uint32_t)gd.fib_rows[o0 + i] * (uint32_t)(MPX_DDS_COLS * sizeof(double));
+            mp = rows + g.max_rows;
+        }
+    }
+    if (active) {
+        int r = warp;
+        for (; r + 3 * DDS_WARPS < nrows; r += 4 * DDS_WARPS) {       // four gathers in flight
+            const int i0 = g.slice_rows[r0 + r], i1 = g.slice_rows[r0 + r + DDS_WARPS];
+            const int i2 = g.slice_rows[r0 + r + 2 * DDS_WARPS], i3 = g.slice_rows[r0 + r + 3 * DDS_WARPS];
+            const double x0 = vals[(int64_t)i0 * ld + col], x1 = vals[(int64_t)i1 * ld + col];
+            const double x2 = vals[(int64_t)i2 * ld + col], x3 = vals[(int64_t)i3 * ld + col];
+            v[(size_t)r * MPX_DDS_COLS + lane] = x0;
+            v[(size_t)(r + DDS_WARPS) * MPX_DDS_COLS + lane] = x1;
+            v[(size_t)(r + 2 * DDS_WARPS) * MPX_DDS_COLS + lane] = x2;
+            v[(size_t)(r + 3 * DDS_WARPS) * MPX_DDS_COLS + lane] = x3;
+        }
+        for (; r < nrows; r += DDS_WARPS)
+            v[(size_t)r * MPX_DDS_COLS + lane] = vals[(int64_t)g.slice_rows[r0 + r] * ld + col];
+    }
+    __syncthreads();
+    unsigned char *vlane = reinterpret_cast<unsigned char *>(v + lane);
+    toff = 0;
+    const uint32_t *mp = meta;
+    for (int t = 0; t < g.n_dims; ++t) {
+        const DdsDimArgs &gd = g.dim[t];
+        const int L = gd.L;
+        const double *df = stab + toff;
+        const double *ry = df + L * L;
+        const int nf = gd.slice_fib0[s + 1] - gd.slice_fib0[s];
+        const uint32_t *foff = mp;
+        const uint32_t *frows = mp + g.max_fibers[t] + 1;
+        if (active) {
+            for (int f = warp; f < nf; f += DDS_WARPS) {
+                const uint32_t *fidx = frows + foff[f];
+                const int len = (int)(foff[f + 1] - foff[f]);
+                // column-wise sweep: for a fixed i the updates of r = i..len-1 are independent,
+                // four of them are kept in flight
+                for (int i = 1; i < len; ++i) {
+                    const double pv = *reinterpret_cast<double *>(vlane + fidx[i - 1]);
+                    const double *dfi = df + (i - 1) * L, *ryi = ry + (i - 1) * L;
+                    int r = i;
+                    for (; r + 3 < len; r += 4) {
+                        double *p0 = reinterpret_cast<double *>(vlane + fidx[r]);
+                        double *p1 = reinterpret_cast<double *>(vlane + fidx[r + 1]);
+                        double *p2 = reinterpret_cast<double *>(vlane + fidx[r + 2]);
+                        double *p3 = reinterpret_cast<double *>(vlane + fidx[r + 3]);
+                        const double x0 = *p0, x1 = *p1, x2 = *p2, x3 = *p3;
+                        const double y0 = dds_update<FAST>(x0, pv, dfi[r], ryi[r]);
+                        const double y1 = dds_update<FAST>(x1, pv, dfi[r + 1], ryi[r + 1]);
+                        const double y2 = dds_update<FAST>(x2, pv, dfi[r + 2], ryi[r + 2]);
+                        const double y3 = dds_update<FAST>(x3, pv, dfi[r + 3], ryi[r + 3]);
+                        *p0 = y0; *p1 = y1; *p2 = y2; *p3 = y3;
+                    }
+                    for (; r < len; ++r) {
+                        double *p0 = reinterpret_cast<double *>(vlane + fidx[r]);
+                        *p0 = dds_update<FAST>(*p0, pv, dfi[r], ryi[r]);
+                    }
+                }
+            }
+        }
+        toff += 2 * L * L;
+        mp = frows + g.max_rows;
+        __syncthreads();
+    }
+    if (active)
+        for (int r = warp; r < nrows; r += DDS_WARPS)
+            vals[(int64_t)g.slice_rows[r0 + r] * ld + col] = v[(size_t)r * MPX_DDS_COLS + lane];
+}
+
 }  // namespace
 
-int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream)
+static int launch_dds_per_dim(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream)
 {
-    if (!pl->complete)
-        return mpx_fail(MPX_ERR_INCOMPLETE,
-                        "trying to use the divided difference scheme with incomplete multi "
-                        "indices, but DDS only works for complete multi indices (without 'holes').");
     for (int d = pl->m - 1; d >= 0; --d) {
         const DdsDim &dd = pl->dds[d];
         if (dd.max_len < 2) continue;
@@ -102,6 +261,47 @@ int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t s
         else
             dds_pass_generic_kernel<<<blocks, tb, 0, stream>>>(vals, ld, k, dd.d_off, dd.d_rows,
                                                                dd.n_fibers, dd.d_diff, dd.max_len);
+        MPX_CUDA(cudaGetLastError());
+    }
+    return MPX_OK;
+}
+
+int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream)
+{
+    if (!pl->complete)
+        return mpx_fail(MPX_ERR_INCOMPLETE,
+                        "trying to use the divided difference scheme with incomplete multi "
+                        "indices, but DDS only works for complete multi indices (without 'holes').");
+    static const bool per_dim = getenv("MPX_DDS_PER_DIM") != nullptr;   // old one-pass-per-dimension path
+    if (per_dim) return launch_dds_per_dim(pl, vals, k, ld, stream);
+    for (const DdsGroup &grp : pl->dds_groups) {
+        DdsGroupArgs a;
+        a.slice_off = grp.d_slice_off;
+        a.slice_rows = grp.d_slice_rows;
+        a.n_dims = (int)grp.dims.size();
+        a.max_rows = grp.max_rows;
+        size_t diff_doubles = 0, meta_words = 0;
+        bool any = false;
+        for (int t = 0; t < a.n_dims; ++t) {
+            const DdsGroupDim &gd = grp.dims[t];
+            a.dim[t] = {gd.d_slice_fib0, gd.d_fib_off, gd.d_fib_rows, gd.d_diff, gd.d_recip, gd.L};
+            a.max_fibers[t] = gd.max_fibers;
+            diff_doubles += (size_t)2 * gd.L * gd.L;
+            meta_words += (size_t)gd.max_fibers + 1 + grp.max_rows;
+            any = any || gd.L >= 2;
+            if (gd.L > DDS_MAX_FIBER) return mpx_fail(MPX_ERR_UNSUPPORTED, "fiber longer than 256");
+        }
+        if (!any) continue;      // every fiber of this group has a single element
+        const size_t smem = ((size_t)grp.max_rows * MPX_DDS_COLS + diff_doubles) * sizeof(double) +
+                            meta_words * sizeof(uint32_t);
+        int smem_max = 0;
+        MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
+        if (smem > (size_t)smem_max) return mpx_fail(MPX_ERR_UNSUPPORTED, "dds slice does not fit shared memory");
+        static const bool force_div = getenv("MPX_DDS_TRUE_DIV") != nullptr;
+        auto fn = (pl->dds_fast_div && !force_div) ? dds_group_kernel<true> : dds_group_kernel<false>;
+        MPX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        dim3 grid((unsigned)grp.n_slices, (unsigned)((k + MPX_DDS_COLS - 1) / MPX_DDS_COLS), 1);
+        fn<<<grid, DDS_WARPS * 32, smem, stream>>>(vals, ld, k, a);
         MPX_CUDA(cudaGetLastError());
     }
     return MPX_OK;

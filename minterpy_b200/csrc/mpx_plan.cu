@@ -4,6 +4,7 @@
 // replaces the per-call preparation of src/minterpy/utils.py:218-231 and the tree metadata
 // of src/minterpy/core/tree.py:47-104 / src/minterpy/dds.py:30-235,473-602.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <numeric>
@@ -199,6 +200,151 @@ int upload(T **dst, const std::vector<T> &src)
     return MPX_OK;
 }
 
+
+// slice id and slice-local position of every row for the dimension group [lo, hi]
+void slice_rows_of_group(const int64_t *e, int64_t N, int m, int lo, int hi,
+                         std::vector<int32_t> &slice_of, std::vector<int32_t> &local_of,
+                         std::vector<int32_t> &slice_off, std::vector<int32_t> &slice_rows)
+{
+    std::vector<int32_t> idx(N);
+    std::iota(idx.begin(), idx.end(), 0);
+    auto outside_less = [&](int32_t a, int32_t b) {
+        for (int i = m - 1; i >= 0; --i) {
+            if (i >= lo && i <= hi) continue;
+            int64_t x = e[(int64_t)a * m + i], y = e[(int64_t)b * m + i];
+            if (x != y) return x < y;
+        }
+        return false;
+    };
+    // stable: rows of one slice keep their lexicographic order
+    std::stable_sort(idx.begin(), idx.end(), outside_less);
+    slice_of.assign(N, 0);
+    local_of.assign(N, 0);
+    slice_off.clear();
+    slice_rows.assign(idx.begin(), idx.end());
+    int32_t s = -1;
+    for (int64_t t = 0; t < N; ++t) {
+        if (t == 0 || outside_less(idx[t - 1], idx[t])) {
+            ++s;
+            slice_off.push_back((int32_t)t);
+        }
+        slice_of[idx[t]] = s;
+        local_of[idx[t]] = (int32_t)(t - slice_off[s]);
+    }
+    slice_off.push_back((int32_t)N);
+    // Small slices are merged with their successors (they stay independent, they just share a
+    // CTA): a CTA should own a few hundred rows so that all its warps find fibers to work on.
+    static const int merge_rows = getenv("MPX_DDS_MERGE_ROWS") ? atoi(getenv("MPX_DDS_MERGE_ROWS")) : MPX_DDS_MERGE_ROWS;
+    std::vector<int32_t> merged_off;
+    int32_t begin = 0;
+    for (size_t t = 0; t + 1 < slice_off.size(); ++t) {
+        const int32_t end = slice_off[t + 1];
+        const bool last = (t + 2 == slice_off.size());
+        const int32_t next_end = last ? end : slice_off[t + 2];
+        if (last || end - begin >= merge_rows || next_end - begin > MPX_DDS_MAX_ROWS) {
+            merged_off.push_back(begin);
+            begin = end;
+        }
+    }
+    merged_off.push_back((int32_t)N);
+    slice_off.swap(merged_off);
+    for (size_t sb = 0; sb + 1 < slice_off.size(); ++sb)
+        for (int32_t t = slice_off[sb]; t < slice_off[sb + 1]; ++t) {
+            slice_of[idx[t]] = (int32_t)sb;
+            local_of[idx[t]] = t - slice_off[sb];
+        }
+}
+
+int build_dds_groups(mpx_plan *pl, const int64_t *e, const std::vector<std::vector<int32_t>> &fibers_off,
+                     const std::vector<std::vector<int32_t>> &fibers_rows, const double *gp_h)
+{
+    const int m = pl->m;
+    const int64_t N = pl->N;
+    std::vector<int32_t> slice_of, local_of, slice_off, slice_rows;
+    int hi = m - 1;
+    while (hi >= 0) {
+        // grow the group downwards while its largest slice still fits shared memory
+        int lo = hi;
+        slice_rows_of_group(e, N, m, lo, hi, slice_of, local_of, slice_off, slice_rows);
+        while (lo > 0) {
+            std::vector<int32_t> so, lo_, sf, sr;
+            slice_rows_of_group(e, N, m, lo - 1, hi, so, lo_, sf, sr);
+            int biggest = 0;
+            for (size_t t = 0; t + 1 < sf.size(); ++t) biggest = std::max(biggest, sf[t + 1] - sf[t]);
+            if (biggest > MPX_DDS_MAX_ROWS) break;
+            --lo;
+            slice_of.swap(so); local_of.swap(lo_); slice_off.swap(sf); slice_rows.swap(sr);
+        }
+        DdsGroup grp;
+        grp.lo = lo;
+        grp.hi = hi;
+        grp.n_slices = (int)slice_off.size() - 1;
+        for (int t = 0; t < grp.n_slices; ++t) grp.max_rows = std::max(grp.max_rows, slice_off[t + 1] - slice_off[t]);
+        if (grp.max_rows > 65535) return mpx_fail(MPX_ERR_UNSUPPORTED, "fiber too long for the dds kernel");
+        int rc;
+        if ((rc = upload(&grp.d_slice_off, slice_off)) != MPX_OK) return rc;
+        if ((rc = upload(&grp.d_slice_rows, slice_rows)) != MPX_OK) return rc;
+        for (int d = hi; d >= lo; --d) {
+            const std::vector<int32_t> &off = fibers_off[d], &rows = fibers_rows[d];
+            const int nf = (int)off.size() - 1;
+            // fibers of dimension d, ordered by the slice they live in
+            std::vector<int32_t> forder(nf);
+            std::iota(forder.begin(), forder.end(), 0);
+            std::stable_sort(forder.begin(), forder.end(), [&](int32_t a, int32_t b) {
+                return slice_of[rows[off[a]]] < slice_of[rows[off[b]]];
+            });
+            std::vector<int32_t> fib0(grp.n_slices + 1, 0), foff;
+            std::vector<uint16_t> frows;
+            frows.reserve(N);
+            int L = 1;
+            for (int t = 0; t < nf; ++t) {
+                const int f = forder[t];
+                fib0[slice_of[rows[off[f]]] + 1]++;
+                foff.push_back((int32_t)frows.size());
+                for (int32_t q = off[f]; q < off[f + 1]; ++q) frows.push_back((uint16_t)local_of[rows[q]]);
+                L = std::max(L, off[f + 1] - off[f]);
+            }
+            foff.push_back((int32_t)frows.size());
+            int max_fibers = 0;
+            for (int t = 0; t < grp.n_slices; ++t) {
+                max_fibers = std::max(max_fibers, fib0[t + 1]);
+                fib0[t + 1] += fib0[t];
+            }
+            std::vector<double> diff((size_t)L * L, 1.0), recip((size_t)L * L, 1.0);
+            for (int l = 0; l < L; ++l)
+                for (int r = 0; r < L; ++r)
+                    if (r != l) {
+                        const double dv = gp_h[(size_t)r * m + d] - gp_h[(size_t)l * m + d];
+                        diff[(size_t)l * L + r] = dv;
+                        // The reciprocal + one correction division returns the IEEE quotient
+                        // only for ordinary divisors: moderate exponent, significand not all
+                        // ones (e.g. 1 - 6e-17 between Chebyshev points DOES occur).  Others
+                        // get reciprocal 0, which sends the kernel to the true division.
+                        uint64_t bits;
+                        std::memcpy(&bits, &dv, 8);
+                        const int ex = (int)((bits >> 52) & 0x7ff);
+                        const uint64_t mant = bits & 0xfffffffffffffull;
+                        const bool ordinary = ex >= 1023 - 200 && ex <= 1023 + 200 &&
+                                              mant != 0xfffffffffffffull;
+                        recip[(size_t)l * L + r] = ordinary ? 1.0 / dv : 0.0;   // host division: RN(1/d)
+                    }
+            DdsGroupDim gd;
+            gd.dim = d;
+            gd.L = L;
+            gd.max_fibers = max_fibers;
+            if ((rc = upload(&gd.d_slice_fib0, fib0)) != MPX_OK) return rc;
+            if ((rc = upload(&gd.d_fib_off, foff)) != MPX_OK) return rc;
+            if ((rc = upload(&gd.d_fib_rows, frows)) != MPX_OK) return rc;
+            if ((rc = upload(&gd.d_diff, diff)) != MPX_OK) return rc;
+            if ((rc = upload(&gd.d_recip, recip)) != MPX_OK) return rc;
+            grp.dims.push_back(gd);
+        }
+        pl->dds_groups.push_back(std::move(grp));
+        hi = lo - 1;
+    }
+    return MPX_OK;
+}
+
 }  // namespace
 
 extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N, int m,
@@ -294,6 +440,7 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
     if ((rc = upload(&pl->d_max_exp, mxv)) != MPX_OK) return rc;
 
     // fiber tables for the divided differences
+    std::vector<std::vector<int32_t>> fibers_off(m), fibers_rows(m);
     if (complete) {
         pl->dds.resize(m);
         std::vector<int64_t> succ(N);
@@ -326,8 +473,11 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
             if ((rc = upload(&dd.d_off, off)) != MPX_OK) return rc;
             if ((rc = upload(&dd.d_rows, rows)) != MPX_OK) return rc;
             if ((rc = upload(&dd.d_diff, diff)) != MPX_OK) return rc;
+            fibers_off[d] = std::move(off);
+            fibers_rows[d] = std::move(rows);
         }
     }
+    if (complete && (rc = build_dds_groups(pl, e, fibers_off, fibers_rows, gp_h)) != MPX_OK) return rc;
     guard.release();
     *plan_out = pl;
     return MPX_OK;
@@ -351,6 +501,17 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
     }
     cudaFree(pl->h_c);
     if (pl->h_event) cudaEventDestroy(pl->h_event);
+    for (DdsGroup &g : pl->dds_groups) {
+        cudaFree(g.d_slice_off);
+        cudaFree(g.d_slice_rows);
+        for (DdsGroupDim &gd : g.dims) {
+            cudaFree(gd.d_slice_fib0);
+            cudaFree(gd.d_fib_off);
+            cudaFree(gd.d_fib_rows);
+            cudaFree(gd.d_diff);
+            cudaFree(gd.d_recip);
+        }
+    }
     for (DdsDim &dd : pl->dds) {
         cudaFree(dd.d_off);
         cudaFree(dd.d_rows);

@@ -51,10 +51,20 @@ def main():
                 except ValueError:
                     pass
     src = page(rep, "source")
-    if len(src) > 2 and "# Samples" in src[1]:
-        h = src[1]
-        data = src[2:]
+    # one section per profiled launch: ["Kernel Name", name], header row, data rows
+    sections, cur = [], None
+    for row in src:
+        if row and row[0] == "Kernel Name":
+            cur = {"name": row[1] if len(row) > 1 else "?", "rows": []}
+            sections.append(cur)
+        elif cur is not None:
+            cur["rows"].append(row)
+    for sec in sections:
+        if len(sec["rows"]) < 2 or "# Samples" not in sec["rows"][0]:
+            continue
+        h = sec["rows"][0]
         si, ie = h.index("# Samples"), h.index("Instructions Executed")
+        data = [r for r in sec["rows"][1:] if len(r) > max(si, ie)]
         tot = sum(int(r[si]) for r in data) or 1
         ti = sum(int(r[ie]) for r in data) or 1
         ops_s, ops_i = collections.Counter(), collections.Counter()
@@ -65,7 +75,8 @@ def main():
             op = (t[1] if t[0].startswith("@") and len(t) > 1 else t[0]).split(".")[0]
             ops_s[op] += int(r[si])
             ops_i[op] += int(r[ie])
-        lines += ["", f"opcode mix (warp instructions executed {ti}, stall samples {tot}):"]
+        lines += ["", f"== source view: {sec['name']}",
+                  f"opcode mix (warp instructions executed {ti}, stall samples {tot}):"]
         for op, n in ops_i.most_common(14):
             lines.append(f"  {op:8s} {100 * n / ti:5.1f}% of instructions   {100 * ops_s[op] / tot:5.1f}% of samples")
         lines += ["", "hottest SASS lines by stall samples:"]
