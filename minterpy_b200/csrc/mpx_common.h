@@ -13,9 +13,9 @@
 // The index set is compiled once per plan into chunks.  One chunk = a fixed-size block of
 // leaf records (descriptor words) plus the coefficient slots those leaves consume, so a CTA
 // can stream chunk after chunk through shared memory with two bulk copies per chunk.
-constexpr int MPX_DESC_WORDS = 256;   // u32 per chunk: [0]=number of words used, [4..] records
+constexpr int MPX_DESC_WORDS = 512;   // u32 per chunk: [0]=number of words used, [4..] records
 constexpr int MPX_DESC_HDR = 4;
-constexpr int MPX_COEF_CAP = 512;     // coefficient slots (doubles) per chunk and polynomial
+constexpr int MPX_COEF_CAP = 1024;    // coefficient slots (doubles) per chunk and polynomial
 constexpr int MPX_STAGES = 8;         // shared-memory ring depth of the chunk stream
 constexpr int MPX_MAX_L0 = 66;        // dimension-0 table entries a thread can hold in registers
 constexpr int MPX_MAX_M = 16;

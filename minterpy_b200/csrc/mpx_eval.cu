@@ -164,7 +164,8 @@ struct LengthChain {
 //   [0, 128)                     mbarriers: full[], empty[]
 //   [128, 128 + S*STAGE_BYTES)   ring: per stage desc words then coefficients
 //   then gp (m*gp_rows doubles), T1 ((max_exp1+1)*R*NT doubles),
-//   upper-level state running product / partial sum (2 * U * R * NT doubles)
+//   running product / partial sum of dimensions 3.. (2 * (U-1) * R * NT doubles; dimension 2
+//   keeps its pair in registers)
 template <int L0P, int R, int A, int NT, int MINB>
 __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
 {
@@ -181,8 +182,8 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
     double *gps = reinterpret_cast<double *>(ring + S * STAGE_BYTES);
     double *T1s = gps + ((m * p.gp_rows + 1) & ~1);
     const int me1 = (m >= 2) ? p.max_exp[1] : 0;
-    double *ups = T1s + (size_t)(me1 + 1) * R * NT;   // [2][U][R][NT]: running product, sum
-    const size_t up_stride = (size_t)U * R * NT;
+    double *ups = T1s + (size_t)(me1 + 1) * R * NT;   // [2][U-1][R][NT]: running product, sum
+    const size_t up_stride = (size_t)(U > 1 ? U - 1 : 0) * R * NT;   // dimensions 3.. only
 
     const int q = blockIdx.y;                                   // polynomial
     const double *coef_img = p.coef + (size_t)q * p.n_chunks * MPX_COEF_CAP;
@@ -218,6 +219,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
     const int64_t tile0 = (int64_t)blockIdx.x * (R * NT);
     double T0[R][L0P];
     double acc1[R];
+    double t2[R], a2[R];          // running product and partial sum of dimension 2
     const double *xrow[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -247,10 +249,15 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
             double t = 1.0;
 #pragma unroll 1
             for (int j = 0; j < p.start_exp[2 + u]; ++j) t *= xu - gps[(2 + u) * p.gp_rows + j];
-            const size_t o = ((size_t)u * R + r) * NT + tid;
-            ups[o] = t;
-            ups[up_stride + o] = 0.0;
+            if (u == 0) {
+                t2[r] = t;               // dimension 2 is folded into often: registers
+            } else {
+                const size_t o = ((size_t)(u - 1) * R + r) * NT + tid;
+                ups[o] = t;
+                ups[up_stride + o] = 0.0;
+            }
         }
+        a2[r] = 0.0;
         acc1[r] = 0.0;
     }
     // (each thread only ever touches its own T1s / ups entries: no barrier needed)
@@ -309,57 +316,90 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                     low[r] = acc1[r];
                     acc1[r] = 0.0;
                 }
-#pragma unroll 1
-                for (int u = 0; u < nf - 1; ++u) {
-                    // level complete as well: hand its sum upwards and restart it
-                    double *ut = ups + (size_t)u * R * NT + tid;
-                    double tv[R], av[R];
+                if (nf == 1) {
+                    // the common fold: dimension 2 takes the sum and moves on (registers only)
+                    const double g2 = gps[2 * p.gp_rows + cur];
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
-                        tv[r] = ut[r * NT];
-                        av[r] = ut[up_stride + r * NT];
+                        a2[r] = fma(t2[r], low[r], a2[r]);
+                        if (!last) t2[r] *= xadv[r] - g2;
                     }
-                    const int st = irregular ? (int)dw[i + 1 + u] : 0;
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        low[r] = fma(tv[r], low[r], av[r]);
-                        double tn = 1.0;
-                        if (st) {
-                            const double xu = xrow[r][2 + u];
-#pragma unroll 1
-                            for (int j = 0; j < st; ++j) tn *= xu - gps[(2 + u) * p.gp_rows + j];
-                        }
-                        ut[up_stride + r * NT] = 0.0;
-                        ut[r * NT] = tn;
-                    }
-                }
-                {
-                    const int u = nf - 1;
-                    double *ut = ups + (size_t)u * R * NT + tid;
-                    const double g = gps[(2 + u) * p.gp_rows + cur];
-                    double tv[R], av[R];
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        tv[r] = ut[r * NT];
-                        av[r] = ut[up_stride + r * NT];
-                    }
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        av[r] = fma(tv[r], low[r], av[r]);
-                        tv[r] *= xadv[r] - g;
-                    }
-                    if (adv > 1) {
+                    if (adv > 1 && !last) {
 #pragma unroll 1
                         for (int j = 1; j < adv; ++j) {
-                            const double gj = gps[(2 + u) * p.gp_rows + cur + j];
+                            const double gj = gps[2 * p.gp_rows + cur + j];
 #pragma unroll
-                            for (int r = 0; r < R; ++r) tv[r] *= xadv[r] - gj;
+                            for (int r = 0; r < R; ++r) t2[r] *= xadv[r] - gj;
                         }
                     }
+                } else {
+                    // dimension 2 is complete as well: hand its sum upwards and restart it
+                    {
+                        const int st = irregular ? (int)dw[i + 1] : 0;
 #pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        ut[up_stride + r * NT] = av[r];
-                        if (!last) ut[r * NT] = tv[r];
+                        for (int r = 0; r < R; ++r) {
+                            low[r] = fma(t2[r], low[r], a2[r]);
+                            a2[r] = 0.0;
+                            double tn = 1.0;
+                            if (st) {
+                                const double xu = xrow[r][2];
+#pragma unroll 1
+                                for (int j = 0; j < st; ++j) tn *= xu - gps[2 * p.gp_rows + j];
+                            }
+                            t2[r] = tn;
+                        }
+                    }
+#pragma unroll 1
+                    for (int u = 1; u < nf - 1; ++u) {
+                        double *ut = ups + (size_t)(u - 1) * R * NT + tid;
+                        double tv[R], av[R];
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            tv[r] = ut[r * NT];
+                            av[r] = ut[up_stride + r * NT];
+                        }
+                        const int st = irregular ? (int)dw[i + 1 + u] : 0;
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            low[r] = fma(tv[r], low[r], av[r]);
+                            double tn = 1.0;
+                            if (st) {
+                                const double xu = xrow[r][2 + u];
+#pragma unroll 1
+                                for (int j = 0; j < st; ++j) tn *= xu - gps[(2 + u) * p.gp_rows + j];
+                            }
+                            ut[up_stride + r * NT] = 0.0;
+                            ut[r * NT] = tn;
+                        }
+                    }
+                    {
+                        const int u = nf - 1;
+                        double *ut = ups + (size_t)(u - 1) * R * NT + tid;
+                        const double g = gps[(2 + u) * p.gp_rows + cur];
+                        double tv[R], av[R];
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            tv[r] = ut[r * NT];
+                            av[r] = ut[up_stride + r * NT];
+                        }
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            av[r] = fma(tv[r], low[r], av[r]);
+                            tv[r] *= xadv[r] - g;
+                        }
+                        if (adv > 1) {
+#pragma unroll 1
+                            for (int j = 1; j < adv; ++j) {
+                                const double gj = gps[(2 + u) * p.gp_rows + cur + j];
+#pragma unroll
+                                for (int r = 0; r < R; ++r) tv[r] *= xadv[r] - gj;
+                            }
+                        }
+#pragma unroll
+                        for (int r = 0; r < R; ++r) {
+                            ut[up_stride + r * NT] = av[r];
+                            if (!last) ut[r * NT] = tv[r];
+                        }
                     }
                 }
                 if (irregular) i += nf;
@@ -373,8 +413,8 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
     for (int r = 0; r < R; ++r) {
         const int64_t pt = tile0 + (int64_t)r * NT + tid;
         if (pt < p.P) {
-            const double res =
-                (U > 0) ? ups[up_stride + ((size_t)(U - 1) * R + r) * NT + tid] : acc1[r];
+            const double res = (U == 0) ? acc1[r] : (U == 1) ? a2[r]
+                               : ups[up_stride + ((size_t)(U - 2) * R + r) * NT + tid];
             p.out[pt * p.ld_out + q] = res;
         }
     }
@@ -397,7 +437,7 @@ size_t eval_smem_bytes(const mpx_plan *pl, int R, int NT, int stages)
     const int U = m > 2 ? m - 2 : 0;
     const int me1 = m >= 2 ? pl->max_exp[1] : 0;
     size_t doubles = (size_t)((m * pl->gp_rows + 1) & ~1) + (size_t)(me1 + 1) * R * NT +
-                     (size_t)2 * U * R * NT;
+                     (size_t)2 * (U > 1 ? U - 1 : 0) * R * NT;
     return 128 + (size_t)stages * STAGE_BYTES + doubles * 8;
 }
 

@@ -11,7 +11,7 @@ import numpy as np
 
 from minterpy_b200 import _lib
 
-DESC_WORDS, DESC_HDR, COEF_CAP = 256, 4, 512
+DESC_WORDS, DESC_HDR, COEF_CAP = 512, 4, 1024
 D_IRREG, D_LAST = 1 << 12, 1 << 13
 
 
