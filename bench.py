@@ -323,9 +323,19 @@ def main():
             peak = peak_dfma or NOMINAL_FP64_TFLOPS
         algo = min(model, executed)
         kernel_ms = float(np.median(step_ms))
+        # DRAM bytes per launch from the committed ncu --set full capture of this workload
+        # (profiles/traffic.json), scaled to the points of this run; null if never captured
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+            if tj and not tensor_path:
+                traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) * P / tj["points"]
+        except (OSError, ValueError, KeyError):
+            traffic = None
         achieved = algo * P / (kernel_ms * 1e-3) / 1e12
         roofline = {"bound": "tensor" if tensor_path else "fp64", "achieved": achieved,
-                    "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                    "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                    "algorithmic_bytes": P * 8 * (m + k),
                     "peak_source": (("measured DMMA (mma.sync f64) rate" if tensor_path else
                                      "measured DFMA rate") + ", tools/fp64_peak.cu on this GPU"
                                     if peak_dfma else "nominal (fp64_peak tool missing)"),

@@ -284,6 +284,14 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
         uint32_t cp = smem_u32(ring + s * STAGE_BYTES + MPX_DESC_WORDS * 4);
         const int iend = MPX_DESC_HDR + (int)dw[0];
         for (int i = MPX_DESC_HDR; i < iend;) {
+            if (next_load < p.n_chunks) {
+                // thread 0, between records: hand a released stage straight back to the TMA
+                const int sp = next_load % S;
+                if (mbar_test(&empty[sp], (uint32_t)(next_load / S - 1) & 1u)) {
+                    issue_load(next_load);
+                    ++next_load;
+                }
+            }
             const uint32_t w = dw[i];
             uint32_t counts[NCW];
 #pragma unroll
