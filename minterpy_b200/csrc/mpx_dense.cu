@@ -2,16 +2,19 @@
 //   replaces MatrixOperator.__matmul__, src/minterpy/schemes/matrix_operator.py:13-22.
 // T is (rows x cols); for the transformations of this path it is N x N, read once from HBM
 // (8 N^2 bytes) and that read bounds the kernel for every k the library meets.  A CTA owns
-// 64 rows; a warp owns 8 of them and sweeps the columns in strips of 32 (coalesced 256 B row
-// segments), each lane keeping KT partial sums per row, reduced by shuffles at the end.
+// 32 rows; a warp owns 4 of them and sweeps the columns, each lane keeping KT partial sums per
+// row, reduced by shuffles at the end.
 #include "mpx_common.h"
 
 namespace {
 
-constexpr int ROWS_PER_WARP = 8;
+constexpr int ROWS_PER_WARP = 4;
 constexpr int WARPS = 8;
-constexpr int KT = 4;   // columns of c per pass
+constexpr int KT = 4;     // columns of c per pass
+constexpr int UNR = 4;    // column strips of 64 in flight per row (double2 loads)
 
+// lanes sweep the columns two at a time (16-byte loads), UNR strips per row are issued before
+// any of them is used: 4 rows x 4 strips x 16 B = 256 B in flight per lane
 __global__ void __launch_bounds__(WARPS * 32)
 dense_apply_kernel(const double *__restrict__ T, int64_t rows, int64_t cols, int64_t ld_t,
                    const double *__restrict__ c, int k, int64_t ld_c, double *__restrict__ out,
@@ -26,14 +29,43 @@ dense_apply_kernel(const double *__restrict__ T, int64_t rows, int64_t cols, int
     for (int i = 0; i < ROWS_PER_WARP; ++i)
 #pragma unroll
         for (int q = 0; q < KT; ++q) acc[i][q] = 0.0;
-    for (int64_t j = lane; j < cols; j += 32) {
+    const bool vec_ok = ((ld_t & 1) == 0) && ((reinterpret_cast<uintptr_t>(T) & 15) == 0);
+    int64_t j0 = 0;
+    if (vec_ok) {
+        const int64_t span = 64 * UNR;
+        for (; j0 + span <= cols; j0 += span) {
+            double2 t[ROWS_PER_WARP][UNR];
+#pragma unroll
+            for (int i = 0; i < ROWS_PER_WARP; ++i) {
+                const int64_t r = (r0 + i < rows) ? r0 + i : rows - 1;
+#pragma unroll
+                for (int u = 0; u < UNR; ++u)
+                    t[i][u] = __ldcs(reinterpret_cast<const double2 *>(T + r * ld_t + j0 + 64 * u + 2 * lane));
+            }
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                const int64_t j = j0 + 64 * u + 2 * lane;
+                double cx[KT], cy[KT];
+#pragma unroll
+                for (int q = 0; q < KT; ++q) {
+                    cx[q] = (q0 + q < k) ? c[j * ld_c + q0 + q] : 0.0;
+                    cy[q] = (q0 + q < k) ? c[(j + 1) * ld_c + q0 + q] : 0.0;
+                }
+#pragma unroll
+                for (int i = 0; i < ROWS_PER_WARP; ++i)
+#pragma unroll
+                    for (int q = 0; q < KT; ++q)
+                        acc[i][q] = fma(t[i][u].y, cy[q], fma(t[i][u].x, cx[q], acc[i][q]));
+            }
+        }
+    }
+    for (int64_t j = j0 + lane; j < cols; j += 32) {          // remainder / unaligned matrices
         double cv[KT];
 #pragma unroll
         for (int q = 0; q < KT; ++q) cv[q] = (q0 + q < k) ? c[j * ld_c + q0 + q] : 0.0;
 #pragma unroll
         for (int i = 0; i < ROWS_PER_WARP; ++i) {
-            const int64_t r = r0 + i;
-            const double t = (r < rows) ? T[r * ld_t + j] : 0.0;
+            const double t = (r0 + i < rows) ? T[(r0 + i) * ld_t + j] : 0.0;
 #pragma unroll
             for (int q = 0; q < KT; ++q) acc[i][q] = fma(t, cv[q], acc[i][q]);
         }

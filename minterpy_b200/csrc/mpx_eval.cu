@@ -55,22 +55,6 @@ __global__ void pack_coeffs_kernel(const double *__restrict__ coeffs, int64_t ld
     img[(int64_t)q * n_slots + s] = (src >= 0) ? coeffs[(int64_t)src * ld_c + q] : 0.0;
 }
 
-__device__ __forceinline__ double2 lds128(uint32_t addr)
-{
-    // volatile: keeps all coefficient loads of a leaf in front of the length switch, so they
-    // are in flight together instead of one exposed shared-memory latency per pair
-    double2 v;
-    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
-    return v;
-}
-
-__device__ __forceinline__ double lds64(uint32_t addr)
-{
-    double v;
-    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
-    return v;
-}
-
 // T1 (dimension-1 table) in shared memory.  R even: [e][r/2][thread][r%2], so one LDS.128
 // fetches the values of two points (lane stride 16 B, conflict free); R odd: [e][r][thread].
 template <int R, int NT>

@@ -39,7 +39,6 @@ struct MmaParams {
     int m;
     int gp_rows;
     int e1;                  // table entries per dimension (largest exponent + 1)
-    int ts;                  // doubles per point table (odd)
     int max_exp[8];
 };
 
@@ -67,7 +66,10 @@ __global__ void pack_mma_kernel(const double *__restrict__ coeffs, int64_t ld_c,
     img[t] = (c < 8 * nt8 && q < k && j < N) ? coeffs[j * ld_c + q] : 0.0;
 }
 
-template <int NT8, int NW>
+// MP = number of dimensions the monomial product is unrolled for (>= m; dimensions m..MP-1
+// read a table row that holds 1.0, so the k-step stays one branch-free basic block and the
+// compiler can interleave the table reads of one k-step with the tensor ops of another)
+template <int NT8, int NW, int MP>
 __global__ void __launch_bounds__(32 * NW, 1) eval_mma_kernel(const MmaParams p)
 {
     constexpr int RS = 8 * NT8 + 4;
@@ -81,7 +83,7 @@ __global__ void __launch_bounds__(32 * NW, 1) eval_mma_kernel(const MmaParams p)
     double *tab = gps + ((p.m * p.gp_rows + 1) & ~1);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int m = p.m, E1 = p.e1, TS = p.ts;
+    const int m = p.m, E1 = p.e1;
     const int tile = blockIdx.y;
     const double *coef_img = p.coef + (size_t)tile * p.n_chunks * (KC * RS);
 
@@ -109,22 +111,27 @@ __global__ void __launch_bounds__(32 * NW, 1) eval_mma_kernel(const MmaParams p)
         next_load = p.n_chunks;
     }
 
-    // product tables of this CTA's points: tab[point][dim][e], thread = point
+    // product tables of this CTA's points: tab[dim][e][point], thread = point.  The point
+    // stride PS = points + 4 keeps the fragment reads below conflict free: the 4 monomials of
+    // a k-step usually differ in one exponent only (rows 8 words apart mod 32), the 4 points of
+    // a half-warp are 2 words apart.
+    constexpr int PS = NTH + 4;
     const int64_t p0 = (int64_t)blockIdx.x * NTH;
     {
         int64_t pt = p0 + tid;
         if (pt >= p.P) pt = p.P - 1;
         const double *xp = p.xx + pt * p.ld_xx;
-        double *T = tab + (size_t)tid * TS;
-        for (int i = 0; i < m; ++i) {
+        for (int i = 0; i < MP; ++i) {
+            double *T = tab + (size_t)i * E1 * PS + tid;
+            T[0] = 1.0;
+            if (i >= m) continue;                        // padding dimension: exponent is always 0
             const double x = xp[i];
             double prod = 1.0;
-            T[i * E1] = 1.0;
             for (int j = 0; j < p.max_exp[i]; ++j) {     // jit_compiled_utils.py:102-112
                 prod *= x - gps[i * p.gp_rows + j];
-                T[i * E1 + j + 1] = prod;
+                T[(size_t)(j + 1) * PS] = prod;
             }
-            for (int j = p.max_exp[i] + 1; j < E1; ++j) T[i * E1 + j] = 0.0;
+            for (int j = p.max_exp[i] + 1; j < E1; ++j) T[(size_t)j * PS] = 0.0;
         }
     }
     __syncthreads();
@@ -136,7 +143,7 @@ __global__ void __launch_bounds__(32 * NW, 1) eval_mma_kernel(const MmaParams p)
         for (int nt = 0; nt < NT8; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = 0.0;
 
     const int jl = lane & 3, g = lane >> 2;
-    const double *Tw = tab + (size_t)(warp * 32 + g) * TS;   // point g of m-tile 0; +8*TS per m-tile
+    const double *tw = tab + warp * 32 + g;                  // point g of m-tile 0; +8 per m-tile
 
     for (int c = 0; c < p.n_chunks; ++c) {
         const int s = c % MMA_STAGES;
@@ -157,19 +164,20 @@ __global__ void __launch_bounds__(32 * NW, 1) eval_mma_kernel(const MmaParams p)
 #pragma unroll 2
         for (int ks = 0; ks < KC / 4; ++ks) {
             const int j = 4 * ks + jl;
-            uint64_t e = ex[j];
+            const uint2 e = *reinterpret_cast<const uint2 *>(ex + j);   // 8 exponents, one byte each
             // monomial value for the 4 points of this lane, reference order i = 0..m-1
             double a[4];
             {
-                const int e0 = (int)(e & 255);
+                const double *row = tw + (e.x & 255u) * (uint32_t)PS;
 #pragma unroll
-                for (int mt = 0; mt < 4; ++mt) a[mt] = Tw[(size_t)mt * 8 * TS + e0];
+                for (int mt = 0; mt < 4; ++mt) a[mt] = row[8 * mt];
             }
-            for (int i = 1; i < m; ++i) {
-                e >>= 8;
-                const int off = i * E1 + (int)(e & 255);
 #pragma unroll
-                for (int mt = 0; mt < 4; ++mt) a[mt] *= Tw[(size_t)mt * 8 * TS + off];
+            for (int i = 1; i < MP; ++i) {
+                const uint32_t ei = ((i < 4 ? e.x : e.y) >> (8 * (i & 3))) & 255u;
+                const double *row = tw + ((uint32_t)(i * E1) + ei) * (uint32_t)PS;
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt) a[mt] *= row[8 * mt];
             }
             const double *brow = cf + j * RS + g;
 #pragma unroll
@@ -197,29 +205,55 @@ __global__ void __launch_bounds__(32 * NW, 1) eval_mma_kernel(const MmaParams p)
     }
 }
 
-template <int NT8, int NW>
-int launch_variant(mpx_plan *pl, const MmaParams &prm, int tiles, size_t smem, cudaStream_t stream)
+template <int NT8, int NW, int MP>
+int launch_variant(const MmaParams &prm, int tiles, size_t smem, cudaStream_t stream)
 {
-    auto fn = &eval_mma_kernel<NT8, NW>;
+    auto fn = &eval_mma_kernel<NT8, NW, MP>;
     MPX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ptiles = (prm.P + 32 * NW - 1) / (32 * NW);
     if (ptiles > 0x7fffffffLL || tiles > 65535)
         return mpx_fail(MPX_ERR_UNSUPPORTED, "too many points or polynomials for one launch");
-    (void)pl;
     fn<<<dim3((unsigned)ptiles, (unsigned)tiles, 1), 32 * NW, smem, stream>>>(prm);
     MPX_CUDA(cudaGetLastError());
     return MPX_OK;
 }
 
-}  // namespace
+template <int NT8, int NW>
+int launch_mp(int mp, const MmaParams &prm, int tiles, size_t smem, cudaStream_t stream)
+{
+    switch (mp) {
+    case 2: return launch_variant<NT8, NW, 2>(prm, tiles, smem, stream);
+    case 3: return launch_variant<NT8, NW, 3>(prm, tiles, smem, stream);
+    case 4: return launch_variant<NT8, NW, 4>(prm, tiles, smem, stream);
+    case 5: return launch_variant<NT8, NW, 5>(prm, tiles, smem, stream);
+    case 6: return launch_variant<NT8, NW, 6>(prm, tiles, smem, stream);
+    default: return launch_variant<NT8, NW, 8>(prm, tiles, smem, stream);
+    }
+}
 
 // polynomials per CTA tile for k polynomials: 8, 16, 32 or 64
-static int mma_nt8_for(int k) { return k <= 8 ? 1 : k <= 16 ? 2 : k <= 32 ? 4 : 8; }
+int mma_nt8_for(int k) { return k <= 8 ? 1 : k <= 16 ? 2 : k <= 32 ? 4 : 8; }
+constexpr size_t MMA_SMEM_LIMIT = 227 * 1024;
+int mma_padded_dims(int m) { return m <= 2 ? 2 : m <= 6 ? m : 8; }
+size_t mma_smem_bytes(const mpx_plan *pl, int nt8, int nw)
+{
+    int e1 = 1;
+    for (int i = 0; i < pl->m; ++i) e1 = std::max(e1, pl->max_exp[i] + 1);
+    const int rs = 8 * nt8 + 4;
+    return (size_t)128 + (size_t)MMA_STAGES * (KC * 8 + KC * rs * 8) +
+           (size_t)((pl->m * pl->gp_rows + 1) & ~1) * 8 +
+           (size_t)mma_padded_dims(pl->m) * e1 * (32 * nw + 4) * 8;
+}
+
+}  // namespace
+
 
 bool mpx_mma_eligible(const mpx_plan *pl, int k)
 {
     static const int min_k = getenv("MPX_EVAL_MMA_MIN_K") ? atoi(getenv("MPX_EVAL_MMA_MIN_K")) : 8;
-    return k >= min_k && pl->m <= 8 && pl->d_exp64 != nullptr;
+    // the product tables of at least 64 points must fit shared memory, else the tree kernel runs
+    return k >= min_k && pl->m <= 8 && pl->d_exp64 != nullptr &&
+           mma_smem_bytes(pl, mma_nt8_for(k), 2) <= MMA_SMEM_LIMIT;
 }
 
 size_t mpx_mma_scratch_bytes(const mpx_plan *pl, int k)
@@ -254,25 +288,14 @@ int mpx_launch_eval_mma(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx
     for (int i = 0; i < pl->m; ++i) { prm.max_exp[i] = pl->max_exp[i]; e1 = std::max(e1, pl->max_exp[i] + 1); }
     for (int i = pl->m; i < 8; ++i) prm.max_exp[i] = 0;
     prm.e1 = e1;
-    prm.ts = (pl->m * e1) | 1;
 
-    int smem_max = 0;
-    MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
-    auto smem_for = [&](int nw) {
-        return (size_t)128 + (size_t)MMA_STAGES * (KC * 8 + KC * rs * 8) +
-               (size_t)((pl->m * pl->gp_rows + 1) & ~1) * 8 + (size_t)32 * nw * prm.ts * 8;
-    };
-    int nw = 8;
-    while (nw > 1 && smem_for(nw) > (size_t)smem_max) nw >>= 1;
-    const size_t smem = smem_for(nw);
-    if (smem > (size_t)smem_max)
-        return mpx_fail(MPX_ERR_UNSUPPORTED, "tables of this index set do not fit shared memory");
+    const int nw = mma_smem_bytes(pl, nt8, 8) <= MMA_SMEM_LIMIT ? 8 : 2;
+    const size_t smem = mma_smem_bytes(pl, nt8, nw);
+    const int mp = mma_padded_dims(pl->m);
 #define MPX_MMA_CASE(NT8, NW) \
-    if (nt8 == NT8 && nw == NW) return launch_variant<NT8, NW>(pl, prm, tiles, smem, stream);
-    MPX_MMA_CASE(8, 8) MPX_MMA_CASE(8, 4) MPX_MMA_CASE(8, 2) MPX_MMA_CASE(8, 1)
-    MPX_MMA_CASE(4, 8) MPX_MMA_CASE(4, 4) MPX_MMA_CASE(4, 2) MPX_MMA_CASE(4, 1)
-    MPX_MMA_CASE(2, 8) MPX_MMA_CASE(2, 4) MPX_MMA_CASE(2, 2) MPX_MMA_CASE(2, 1)
-    MPX_MMA_CASE(1, 8) MPX_MMA_CASE(1, 4) MPX_MMA_CASE(1, 2) MPX_MMA_CASE(1, 1)
+    if (nt8 == NT8 && nw == NW) return launch_mp<NT8, NW>(mp, prm, tiles, smem, stream);
+    MPX_MMA_CASE(8, 8) MPX_MMA_CASE(8, 2) MPX_MMA_CASE(4, 8) MPX_MMA_CASE(4, 2)
+    MPX_MMA_CASE(2, 8) MPX_MMA_CASE(2, 2) MPX_MMA_CASE(1, 8) MPX_MMA_CASE(1, 2)
 #undef MPX_MMA_CASE
     return mpx_fail(MPX_ERR_UNSUPPORTED, "no tensor-core variant for this shape");
 }
