@@ -74,6 +74,7 @@ struct DdsGroupDim {
     uint16_t *d_fib_rows = nullptr;   // N: slice-local row of every fiber element, e_d ascending
     double *d_diff = nullptr;         // (L x L): diff[l*L + r] = gp[r,dim] - gp[l,dim]
     double *d_recip = nullptr;        // (L x L): 1.0 / diff, correctly rounded (host division)
+    double *d_g = nullptr;            // (L): generating points of this dimension
 };
 struct DdsGroup {
     int lo = 0, hi = 0;
@@ -92,6 +93,7 @@ struct mpx_plan {
     int max_exp[MPX_MAX_M] = {0};
     int start_exp[MPX_MAX_M] = {0};  // exponents of the first leaf in dimensions >= 2
     bool complete = false;
+    bool tree_ok = true;             // dimension-0 exponents fit the register table of the tree kernel
     // evaluation
     EvalProgram prog;
     uint32_t *d_desc = nullptr;

@@ -100,6 +100,7 @@ struct DdsDimArgs {
     const uint16_t *fib_rows;
     const double *diff;
     const double *recip;
+    const double *gcol;
     int L;
 };
 struct DdsGroupArgs {
@@ -131,7 +132,7 @@ __device__ __forceinline__ double dds_update(double x, double pv, double d, doub
         if (ex - 123u < 1800u && __double2hiint(y) != 0) return q2;
         return dds_true_division(a, d);
     } else {
-        return __ddiv_rn(a, d);
+        return __ddiv_rn(a, d);       // here d = g[r] - g[i-1] was formed by the caller
     }
 }
 
@@ -139,7 +140,8 @@ template <bool FAST>
 __global__ void __launch_bounds__(DDS_WARPS * 32)
 dds_group_kernel(double *__restrict__ vals, int64_t ld, int k, const DdsGroupArgs g)
 {
-    // shared memory: v[max_rows][32] | per dim: diff (L*L), recip (L*L) | per dim: fiber
+    // shared memory: v[max_rows][32] | per dim: diff (L*L), recip (L*L)  [FAST]  or g (L) |
+    // per dim: fiber
     // offsets (max_fibers + 1) and fiber rows as byte offsets into v (max_rows), both u32
     extern __shared__ __align__(16) unsigned char dsm[];
     double *v = reinterpret_cast<double *>(dsm);
@@ -152,12 +154,19 @@ dds_group_kernel(double *__restrict__ vals, int64_t ld, int k, const DdsGroupArg
     const int nrows = g.slice_off[s + 1] - r0;
     size_t toff = 0;
     for (int t = 0; t < g.n_dims; ++t) {
-        const int LL = g.dim[t].L * g.dim[t].L;
-        for (int i = threadIdx.x; i < LL; i += blockDim.x) {
-            stab[toff + i] = g.dim[t].diff[i];
-            stab[toff + LL + i] = g.dim[t].recip[i];
+        if constexpr (FAST) {
+            const int LL = g.dim[t].L * g.dim[t].L;
+            for (int i = threadIdx.x; i < LL; i += blockDim.x) {
+                stab[toff + i] = g.dim[t].diff[i];
+                stab[toff + LL + i] = g.dim[t].recip[i];
+            }
+            toff += 2 * LL;
+        } else {
+            // long fibers: no room for L x L tables -- keep the generating points and form
+            // every divisor g[r] - g[i-1] on the fly (the very subtraction the host tabulates)
+            for (int i = threadIdx.x; i < g.dim[t].L; i += blockDim.x) stab[toff + i] = g.dim[t].gcol[i];
+            toff += g.dim[t].L;
         }
-        toff += 2 * LL;
     }
     uint32_t *meta = reinterpret_cast<uint32_t *>(stab + toff);
     {
@@ -196,8 +205,8 @@ dds_group_kernel(double *__restrict__ vals, int64_t ld, int k, const DdsGroupArg
     for (int t = 0; t < g.n_dims; ++t) {
         const DdsDimArgs &gd = g.dim[t];
         const int L = gd.L;
-        const double *df = stab + toff;
-        const double *ry = df + L * L;
+        const double *df = stab + toff;          // FAST: diff table, else the g column
+        const double *ry = df + L * L;           // FAST only
         const int nf = gd.slice_fib0[s + 1] - gd.slice_fib0[s];
         const uint32_t *foff = mp;
         const uint32_t *frows = mp + g.max_fibers[t] + 1;
@@ -209,28 +218,45 @@ dds_group_kernel(double *__restrict__ vals, int64_t ld, int k, const DdsGroupArg
                 // four of them are kept in flight
                 for (int i = 1; i < len; ++i) {
                     const double pv = *reinterpret_cast<double *>(vlane + fidx[i - 1]);
-                    const double *dfi = df + (i - 1) * L, *ryi = ry + (i - 1) * L;
-                    int r = i;
-                    for (; r + 3 < len; r += 4) {
-                        double *p0 = reinterpret_cast<double *>(vlane + fidx[r]);
-                        double *p1 = reinterpret_cast<double *>(vlane + fidx[r + 1]);
-                        double *p2 = reinterpret_cast<double *>(vlane + fidx[r + 2]);
-                        double *p3 = reinterpret_cast<double *>(vlane + fidx[r + 3]);
-                        const double x0 = *p0, x1 = *p1, x2 = *p2, x3 = *p3;
-                        const double y0 = dds_update<FAST>(x0, pv, dfi[r], ryi[r]);
-                        const double y1 = dds_update<FAST>(x1, pv, dfi[r + 1], ryi[r + 1]);
-                        const double y2 = dds_update<FAST>(x2, pv, dfi[r + 2], ryi[r + 2]);
-                        const double y3 = dds_update<FAST>(x3, pv, dfi[r + 3], ryi[r + 3]);
-                        *p0 = y0; *p1 = y1; *p2 = y2; *p3 = y3;
-                    }
-                    for (; r < len; ++r) {
-                        double *p0 = reinterpret_cast<double *>(vlane + fidx[r]);
-                        *p0 = dds_update<FAST>(*p0, pv, dfi[r], ryi[r]);
+                    if constexpr (FAST) {
+                        const double *dfi = df + (i - 1) * L, *ryi = ry + (i - 1) * L;
+                        int r = i;
+                        for (; r + 3 < len; r += 4) {
+                            double *p0 = reinterpret_cast<double *>(vlane + fidx[r]);
+                            double *p1 = reinterpret_cast<double *>(vlane + fidx[r + 1]);
+                            double *p2 = reinterpret_cast<double *>(vlane + fidx[r + 2]);
+                            double *p3 = reinterpret_cast<double *>(vlane + fidx[r + 3]);
+                            const double x0 = *p0, x1 = *p1, x2 = *p2, x3 = *p3;
+                            const double y0 = dds_update<true>(x0, pv, dfi[r], ryi[r]);
+                            const double y1 = dds_update<true>(x1, pv, dfi[r + 1], ryi[r + 1]);
+                            const double y2 = dds_update<true>(x2, pv, dfi[r + 2], ryi[r + 2]);
+                            const double y3 = dds_update<true>(x3, pv, dfi[r + 3], ryi[r + 3]);
+                            *p0 = y0; *p1 = y1; *p2 = y2; *p3 = y3;
+                        }
+                        for (; r < len; ++r) {
+                            double *p0 = reinterpret_cast<double *>(vlane + fidx[r]);
+                            *p0 = dds_update<true>(*p0, pv, dfi[r], ryi[r]);
+                        }
+                    } else {
+                        const double gl = df[i - 1];
+                        int r = i;
+                        for (; r + 1 < len; r += 2) {
+                            double *p0 = reinterpret_cast<double *>(vlane + fidx[r]);
+                            double *p1 = reinterpret_cast<double *>(vlane + fidx[r + 1]);
+                            const double x0 = *p0, x1 = *p1;
+                            const double y0 = dds_update<false>(x0, pv, __dsub_rn(df[r], gl), 0.0);
+                            const double y1 = dds_update<false>(x1, pv, __dsub_rn(df[r + 1], gl), 0.0);
+                            *p0 = y0; *p1 = y1;
+                        }
+                        for (; r < len; ++r) {
+                            double *p0 = reinterpret_cast<double *>(vlane + fidx[r]);
+                            *p0 = dds_update<false>(*p0, pv, __dsub_rn(df[r], gl), 0.0);
+                        }
                     }
                 }
             }
         }
-        toff += 2 * L * L;
+        toff += FAST ? 2 * L * L : L;
         mp = frows + g.max_rows;
         __syncthreads();
     }
@@ -280,25 +306,28 @@ int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t s
         a.slice_rows = grp.d_slice_rows;
         a.n_dims = (int)grp.dims.size();
         a.max_rows = grp.max_rows;
-        size_t diff_doubles = 0, meta_words = 0;
+        size_t diff_doubles = 0, g_doubles = 0, meta_words = 0;
+        static const bool force_div = getenv("MPX_DDS_TRUE_DIV") != nullptr;
+        bool fast = pl->dds_fast_div && !force_div;
         bool any = false;
         for (int t = 0; t < a.n_dims; ++t) {
             const DdsGroupDim &gd = grp.dims[t];
-            a.dim[t] = {gd.d_slice_fib0, gd.d_fib_off, gd.d_fib_rows, gd.d_diff, gd.d_recip, gd.L};
+            a.dim[t] = {gd.d_slice_fib0, gd.d_fib_off, gd.d_fib_rows, gd.d_diff, gd.d_recip, gd.d_g, gd.L};
             a.max_fibers[t] = gd.max_fibers;
+            fast = fast && gd.L <= 40;          // L x L tables of diff and recip must stay small
             diff_doubles += (size_t)2 * gd.L * gd.L;
+            g_doubles += (size_t)gd.L;
             meta_words += (size_t)gd.max_fibers + 1 + grp.max_rows;
             any = any || gd.L >= 2;
             if (gd.L > DDS_MAX_FIBER) return mpx_fail(MPX_ERR_UNSUPPORTED, "fiber longer than 256");
         }
         if (!any) continue;      // every fiber of this group has a single element
-        const size_t smem = ((size_t)grp.max_rows * MPX_DDS_COLS + diff_doubles) * sizeof(double) +
+        const size_t smem = ((size_t)grp.max_rows * MPX_DDS_COLS + (fast ? diff_doubles : g_doubles)) * sizeof(double) +
                             meta_words * sizeof(uint32_t);
         int smem_max = 0;
         MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
         if (smem > (size_t)smem_max) return mpx_fail(MPX_ERR_UNSUPPORTED, "dds slice does not fit shared memory");
-        static const bool force_div = getenv("MPX_DDS_TRUE_DIV") != nullptr;
-        auto fn = (pl->dds_fast_div && !force_div) ? dds_group_kernel<true> : dds_group_kernel<false>;
+        auto fn = fast ? dds_group_kernel<true> : dds_group_kernel<false>;
         MPX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         dim3 grid((unsigned)grp.n_slices, (unsigned)((k + MPX_DDS_COLS - 1) / MPX_DDS_COLS), 1);
         fn<<<grid, DDS_WARPS * 32, smem, stream>>>(vals, ld, k, a);

@@ -444,6 +444,10 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
     if (P == 0 && coeffs == nullptr) return MPX_OK;
     if (mpx_mma_eligible(pl, k))
         return mpx_launch_eval_mma(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
+    if (!pl->tree_ok)
+        return mpx_fail(MPX_ERR_UNSUPPORTED,
+                        "dimension-0 exponent > 64 needs the shared-memory-table kernel, whose tables "
+                        "(m <= 8, m * (largest exponent + 1) * 36 doubles) do not fit for this index set");
     const int l0p = mpx_l0p_for(pl->max_exp[0]);
     // kernel variants: (dimension-0 table size, points per thread, threads per CTA); for each
     // table size the first entry whose shared memory fits is taken

@@ -251,8 +251,9 @@ size_t mma_smem_bytes(const mpx_plan *pl, int nt8, int nw)
 bool mpx_mma_eligible(const mpx_plan *pl, int k)
 {
     static const int min_k = getenv("MPX_EVAL_MMA_MIN_K") ? atoi(getenv("MPX_EVAL_MMA_MIN_K")) : 8;
-    // the product tables of at least 64 points must fit shared memory, else the tree kernel runs
-    return k >= min_k && pl->m <= 8 && pl->d_exp64 != nullptr &&
+    // the product tables of at least 64 points must fit shared memory, else the tree kernel
+    // runs; plans the tree kernel cannot take (dimension-0 exponent > 64) come here for every k
+    return (k >= min_k || !pl->tree_ok) && pl->m <= 8 && pl->d_exp64 != nullptr &&
            mma_smem_bytes(pl, mma_nt8_for(k), 2) <= MMA_SMEM_LIMIT;
 }
 

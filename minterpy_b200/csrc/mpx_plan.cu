@@ -337,6 +337,9 @@ int build_dds_groups(mpx_plan *pl, const int64_t *e, const std::vector<std::vect
             if ((rc = upload(&gd.d_fib_rows, frows)) != MPX_OK) return rc;
             if ((rc = upload(&gd.d_diff, diff)) != MPX_OK) return rc;
             if ((rc = upload(&gd.d_recip, recip)) != MPX_OK) return rc;
+            std::vector<double> gcol(L);
+            for (int l = 0; l < L; ++l) gcol[l] = gp_h[(size_t)l * m + d];
+            if ((rc = upload(&gd.d_g, gcol)) != MPX_OK) return rc;
             grp.dims.push_back(gd);
         }
         pl->dds_groups.push_back(std::move(grp));
@@ -379,9 +382,9 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
             return mpx_fail(MPX_ERR_ARG, "generating_points has fewer rows than the largest exponent");
         maxmax = std::max(maxmax, pl->max_exp[i]);
     }
-    if (pl->max_exp[0] + 1 > MPX_MAX_L0 - 1)
-        return mpx_fail(MPX_ERR_UNSUPPORTED,
-                        "exponent in dimension 0 exceeds 64 (register table of the evaluation kernel)");
+    // beyond 64 the dimension-0 table no longer fits registers: such plans evaluate with the
+    // shared-memory-table kernel (mpx_eval_mma.cu) for every k
+    pl->tree_ok = pl->max_exp[0] + 1 <= MPX_MAX_L0 - 1;
     pl->gp_rows = (int)std::min<int64_t>(gp_rows, maxmax + 1);
 
     // lexicographic order (identity for a MultiIndexSet, which is always sorted)
@@ -407,8 +410,11 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
     pl->complete = complete;
 
     std::string err;
-    int rc = compile_program(e, N, m, order, mpx_l0p_for(pl->max_exp[0]), pl->prog, err);
-    if (rc != MPX_OK) return mpx_fail(rc, err);
+    int rc = MPX_OK;
+    if (pl->tree_ok) {
+        rc = compile_program(e, N, m, order, mpx_l0p_for(pl->max_exp[0]), pl->prog, err);
+        if (rc != MPX_OK) return mpx_fail(rc, err);
+    }
     // upper-level exponents of the first leaf (0 for every downward-closed set)
     for (int i = 2; i < m; ++i) {
         pl->start_exp[i] = (int)e[order[0] * m + i];
@@ -510,6 +516,7 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
             cudaFree(gd.d_fib_rows);
             cudaFree(gd.d_diff);
             cudaFree(gd.d_recip);
+            cudaFree(gd.d_g);
         }
     }
     for (DdsDim &dd : pl->dds) {

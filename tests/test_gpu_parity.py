@@ -293,3 +293,40 @@ def test_tensor_core_path_irregular_and_small(mpb):
         xx = rng.uniform(-1, 1, (int(rng.integers(1, 300)), m))
         got = mpb.Plan(e, gp).eval(xx, c)
         assert rel_err(got, oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL
+
+
+def test_long_dimension0_and_many_dimensions(mpb):
+    """Shapes outside the tree kernel's register table (dimension-0 exponent > 64) run on the
+    shared-memory-table kernel; m up to 16 runs on the tree kernel."""
+    rng = np.random.default_rng(77)
+    # 1-D, degree 150 (Chebyshev-like points), and 2-D with a long first dimension
+    n = 150
+    gp = np.cos(np.pi * np.arange(n + 1) / n).reshape(-1, 1)
+    e = np.arange(n + 1, dtype=np.int64).reshape(-1, 1)
+    c = rng.uniform(-1, 1, (n + 1, 2)) * np.exp(-0.05 * np.arange(n + 1))[:, None]
+    xx = rng.uniform(-1, 1, (500, 1))
+    plan = mpb.Plan(e, gp)
+    assert rel_err(plan.eval(xx, c), oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL
+    assert np.array_equal(plan.dds(c), oracle.dds(c, e, gp))
+    e2 = np.array([[a, b] for b in range(4) for a in range(90 - 20 * b)], dtype=np.int64)
+    gp2 = np.stack([np.cos(np.pi * np.arange(91) / 90), -np.cos(np.pi * np.arange(91) / 90)], axis=1)
+    c2 = rng.uniform(-1, 1, (e2.shape[0], 1))
+    xx2 = rng.uniform(-1, 1, (123, 2))
+    assert rel_err(mpb.Plan(e2, gp2).eval(xx2, c2), oracle.eval_newton_polynomials(xx2, c2, e2, gp2)) <= EVAL_RTOL
+    # many dimensions: total degree 2 in m = 9, 12, 16
+    for m in (9, 12, 16):
+        rows = [[0] * m]
+        for i in range(m):
+            for v in (1, 2):
+                r = [0] * m; r[i] = v; rows.append(r)
+            for j in range(i):
+                r = [0] * m; r[i] = 1; r[j] = 1; rows.append(r)
+        em = np.array(rows, dtype=np.int64)
+        em = em[np.lexsort(em.T)]
+        gpm = np.tile(np.array([[1.0], [-1.0], [0.0]]), (1, m)) * np.where(np.arange(m) % 2 == 0, -1, 1)
+        cm = rng.uniform(-1, 1, (em.shape[0], 3))
+        xm = rng.uniform(-1, 1, (77, m))
+        planm = mpb.Plan(em, gpm)
+        assert rel_err(planm.eval(xm, cm), oracle.eval_newton_polynomials(xm, cm, em, gpm)) <= EVAL_RTOL
+        assert planm.is_complete
+        assert np.array_equal(planm.dds(cm), oracle.dds(cm, em, gpm))
