@@ -455,22 +455,24 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
         {10, 4, 256, kfn<10, 4, 1, 256, 1>()},
         {10, 4, 128, kfn<10, 4, 1, 128, 1>()},
         {10, 4, 64, kfn<10, 4, 1, 64, 1>()},
+        {10, 1, 64, kfn<10, 1, 2, 64, 1>()},      // last resort: very long dimension-1 tables
         {18, 4, 256, kfn<18, 4, 1, 256, 1>()},
         {18, 4, 128, kfn<18, 4, 1, 128, 1>()},
         {18, 4, 64, kfn<18, 4, 1, 64, 1>()},
+        {18, 1, 64, kfn<18, 1, 2, 64, 1>()},
         {34, 2, 256, kfn<34, 2, 2, 256, 1>()},
         {34, 2, 128, kfn<34, 2, 2, 128, 1>()},
         {34, 2, 64, kfn<34, 2, 2, 64, 1>()},
+        {34, 1, 64, kfn<34, 1, 2, 64, 1>()},
         {66, 1, 256, kfn<66, 1, 2, 256, 1>()},
         {66, 1, 128, kfn<66, 1, 2, 128, 1>()},
         {66, 1, 64, kfn<66, 1, 2, 64, 1>()},
         // experimental alternatives, selected with MPX_EVAL_VARIANT=<index>
-        {18, 4, 256, kfn<18, 4, 2, 256, 1>()},   // 12: two accumulators per point
-        {18, 3, 384, kfn<18, 3, 1, 384, 1>()},   // 13: 3 points, 12 warps
-        {18, 2, 512, kfn<18, 2, 1, 512, 1>()},   // 14: 2 points, 16 warps in one CTA
-        {18, 2, 256, kfn<18, 2, 2, 256, 2>()},   // 15: 2 points x 2 accumulators, 2 CTAs/SM
+        {18, 4, 256, kfn<18, 4, 2, 256, 1>()},   // 15: two accumulators per point
+        {18, 3, 384, kfn<18, 3, 1, 384, 1>()},   // 16: 3 points, 12 warps
+        {18, 2, 512, kfn<18, 2, 1, 512, 1>()},   // 17: 2 points, 16 warps in one CTA
     };
-    constexpr int n_standard = 12;
+    constexpr int n_standard = 15;
     int smem_max = 0;
     MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
     // tuning knobs for experiments (defaults are what the library ships with)

@@ -330,3 +330,20 @@ def test_long_dimension0_and_many_dimensions(mpb):
         assert rel_err(planm.eval(xm, cm), oracle.eval_newton_polynomials(xm, cm, em, gpm)) <= EVAL_RTOL
         assert planm.is_complete
         assert np.array_equal(planm.dds(cm), oracle.dds(cm, em, gpm))
+
+
+def test_long_higher_dimensions(mpb):
+    """Small dimension-0 table but very long tables in dimensions 1 and 2 (tree kernel with few
+    points per CTA), k below and above the tensor-core threshold."""
+    rng = np.random.default_rng(78)
+    rows = [[a, b, c] for c in range(0, 3) for b in range(0, 200 - 60 * c, 7) for a in range(3)]
+    rows += [[0, b, 0] for b in range(200) if b % 7]
+    e = np.unique(np.array(rows, dtype=np.int64), axis=0)
+    e = e[np.lexsort(e.T)]
+    pts = np.cos(np.pi * np.arange(201) / 200)
+    gp = np.stack([pts, -pts, pts], axis=1)
+    xx = rng.uniform(-1, 1, (60, 3))
+    for k in (1, 3, 12):
+        c = rng.uniform(-1, 1, (e.shape[0], k)) * 1e-3
+        got = mpb.Plan(e, gp).eval(xx, c)
+        assert rel_err(got, oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL
