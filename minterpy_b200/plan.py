@@ -6,6 +6,7 @@ tensors are passed by ``data_ptr()`` without a copy and results come back as tor
 """
 import ctypes
 import threading
+import zlib
 
 import numpy as np
 
@@ -151,7 +152,9 @@ def get_plan(exponents, generating_points, device=None):
     gp = np.ascontiguousarray(generating_points, dtype=np.float64)
     if device is None:
         device = _current_device()
-    key = (int(device), e.shape, gp.shape, hash(e.tobytes()), hash(gp.tobytes()))
+    # content key: two independent 32-bit checksums per array, computed without copying
+    key = (int(device), e.shape, gp.shape, zlib.crc32(e), zlib.adler32(e), zlib.crc32(gp),
+           zlib.adler32(gp))
     with _cache_lock:
         plan = _cache.get(key)
         if plan is None:

@@ -41,6 +41,12 @@ def main():
     except (OSError, KeyError):
         hbm, src = 6650.0, "fallback"
     stream = torch.cuda.current_stream().cuda_stream
+    # context: what a pure write stream reaches on this GPU (torch fill of 8 GB)
+    buf = torch.empty(1 << 30, dtype=torch.float64, device="cuda")
+    ms = timed(lambda: buf.fill_(1.0))
+    print(json.dumps({"bench": "write_only_fill", "bytes": 8 << 30, "ms": ms,
+                      "GBps": (8 << 30) / (ms * 1e-3) / 1e9, "hbm_copy_peak": hbm}))
+    del buf
     for tag, P in (("cfg2", 40000), ("cfg3", 100000)):
         g = golden_io.load(tag)
         e, gp = g["exponents"], g["generating_points"]
