@@ -332,6 +332,12 @@ def main():
             executed = n_pad * (2 * k_pad + (m - 1)) + 2 * int(e.max(axis=0).sum())
             fma = n_pad * k_pad
             peak = peak_dmma or NOMINAL_FP64_TFLOPS
+        elif plan.info(_lib.INFO_SMALLK_KERNEL) == 1:
+            # tensor-core tree kernel (mpx_eval_tmma.cu): leaf sums as DMMA tiles
+            tensor_path = True
+            fma = plan.info(_lib.INFO_TMMA_FMA) * k
+            executed = 2 * fma + other * k
+            peak = peak_dmma or NOMINAL_FP64_TFLOPS
         else:
             executed = (2 * fma + other) * k          # FP64 flops per point actually issued
             fma = fma * k
@@ -358,7 +364,8 @@ def main():
                     "measured_dmma_peak": peak_dmma,
                     "flops_per_point_model": model, "flops_per_point_executed": executed,
                     "fma_per_point": fma,
-                    "kernel": "eval_mma_kernel" if tensor_path else "eval_tree_kernel",
+                    "kernel": ("eval_mma_kernel" if (k >= 8 and m <= 8) else
+                               "eval_tmma_kernel" if tensor_path else "eval_tree_kernel"),
                     "kernel_ms": kernel_ms,
                     "hbm_gbs": P * 8 * (m + k) / (kernel_ms * 1e-3) / 1e9}
         cpu = None if args.no_cpu else cpu_baseline(e, gp, k)

@@ -71,7 +71,11 @@ enum {
     MPX_INFO_DEVICE = 6,
     MPX_INFO_SCRATCH_BYTES = 7,/* device scratch currently held by the plan                  */
     MPX_INFO_EVAL_OTHER_FP64 = 8, /* FP64 adds/multiplies besides the FMAs, per point        */
-    MPX_INFO_CHUNKS = 9        /* chunks of the evaluation program                           */
+    MPX_INFO_CHUNKS = 9,       /* chunks of the evaluation program                           */
+    MPX_INFO_SMALLK_KERNEL = 10, /* kernel used for k < 8: 0 = DFMA tree, 1 = tensor-core tree,
+                                  2 = shared-memory-table tensor kernel (long dimension 0)   */
+    MPX_INFO_TMMA_FMA = 11     /* FMAs per point and polynomial of the tensor-core tree kernel
+                                  (tile padding included), 0 if it was not built             */
 };
 int mpx_plan_info(const mpx_plan *plan, int what, int64_t *value_out);
 

@@ -33,11 +33,14 @@ SIGNATURES = {
 DEBUG_SIGNATURES = {
     "mpx_debug_program": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, ctypes.POINTER(c_i64),
                                   ctypes.POINTER(c_i64)]),
+    "mpx_debug_tile_program": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, ctypes.POINTER(c_i64),
+                                       ctypes.POINTER(c_i64)]),
 }
 
 MPX_OK, MPX_ERR_ARG, MPX_ERR_INCOMPLETE, MPX_ERR_CUDA, MPX_ERR_UNSUPPORTED, MPX_ERR_NOMEM = range(6)
 (INFO_N, INFO_M, INFO_COMPLETE, INFO_EVAL_FMA, INFO_DDS_UPDATES, INFO_LEAVES, INFO_DEVICE,
- INFO_SCRATCH_BYTES, INFO_EVAL_OTHER_FP64, INFO_CHUNKS) = range(10)
+ INFO_SCRATCH_BYTES, INFO_EVAL_OTHER_FP64, INFO_CHUNKS, INFO_SMALLK_KERNEL,
+ INFO_TMMA_FMA) = range(12)
 
 _lib = None
 

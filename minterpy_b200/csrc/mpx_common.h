@@ -53,6 +53,30 @@ struct EvalProgram {
     std::vector<int32_t> slot_src; // n_chunks * MPX_COEF_CAP, row of the coefficient or -1
 };
 
+// ---- tile program of the tensor-core tree kernel (mpx_eval_tmma.cu) ------------------------
+// For complete index sets the leaf sums  sum_e0 c[leaf][e0] * T0[point][e0]  form a dense
+// contraction [points x e0] * [e0 x leaves] that DMMA m8n8k4 computes 8 leaves at a time.  A
+// TILE is 8 columns (leaves with consecutive dimension-1 exponents; the columns may continue
+// into the head of the next (e2.., e_{m-1}) group) and `ks` k-steps of 4 dimension-0
+// exponents; its coefficients are stored as B fragments: slot = s*32 + column*4 + (e0 & 3).
+// Tile record, two words:
+//   w0 bits 0..4 ks | 5..8 columns of the current group | 9..12 columns of the next group |
+//      13..20 dimension-1 exponent of column 0 | 21 the current group ends in this tile |
+//      22..25 nf (folds into dimensions 2.. when it ends) | 26 last tile of the program
+//   w1 exponent (before advancing) of the level that advances after the fold
+constexpr int MPX_T_DESC_WORDS = 128;   // u32 per chunk: [0] = words used, [4..] records
+constexpr int MPX_T_COEF_CAP = 2048;    // coefficient slots per chunk (64 k-steps)
+struct TileProgram {
+    bool usable = false;          // built (complete set, m >= 2) and not wasteful
+    int n_chunks = 0;
+    int ks_max = 0;               // k-steps the dimension-0 table needs: ceil((max_exp0+1)/4)
+    int64_t n_tiles = 0;
+    int64_t mma_fma_per_point = 0;    // 32 * sum of ks over the tiles (tensor FMAs per point)
+    int64_t fma_per_point = 0;        // + level-1 FMAs (8 per tile) + folds
+    std::vector<uint32_t> desc;       // n_chunks * MPX_T_DESC_WORDS
+    std::vector<int32_t> slot_src;    // n_chunks * MPX_T_COEF_CAP
+};
+
 struct DdsDim {
     int n_fibers = 0;
     int max_len = 0;
@@ -96,6 +120,9 @@ struct mpx_plan {
     bool tree_ok = true;             // dimension-0 exponents fit the register table of the tree kernel
     // evaluation
     EvalProgram prog;
+    TileProgram tprog;               // tensor-core tree kernel (complete sets)
+    uint32_t *d_tdesc = nullptr;
+    int32_t *d_tslot_src = nullptr;
     uint32_t *d_desc = nullptr;
     int32_t *d_slot_src = nullptr;
     double *d_gp = nullptr;          // (m x gp_rows) dimension-major copy of the generating points
@@ -151,5 +178,11 @@ size_t mpx_mma_scratch_bytes(const mpx_plan *plan, int k);
 int mpx_launch_eval_mma(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
                         const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                         cudaStream_t stream);
+// tensor-core tree kernel (complete sets, few polynomials), mpx_eval_tmma.cu
+bool mpx_tmma_eligible(const mpx_plan *plan, int k);
+size_t mpx_tmma_scratch_bytes(const mpx_plan *plan, int k);
+int mpx_launch_eval_tmma(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+                         const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
+                         cudaStream_t stream);
 // bytes of plan scratch an evaluation of k polynomials needs (either path)
 size_t mpx_eval_scratch_bytes(const mpx_plan *plan, int k);

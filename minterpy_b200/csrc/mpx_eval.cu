@@ -444,6 +444,8 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
     if (P == 0 && coeffs == nullptr) return MPX_OK;
     if (mpx_mma_eligible(pl, k))
         return mpx_launch_eval_mma(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
+    if (mpx_tmma_eligible(pl, k))
+        return mpx_launch_eval_tmma(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
     if (!pl->tree_ok)
         return mpx_fail(MPX_ERR_UNSUPPORTED,
                         "dimension-0 exponent > 64 needs the shared-memory-table kernel, whose tables "
@@ -528,5 +530,6 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
 size_t mpx_eval_scratch_bytes(const mpx_plan *pl, int k)
 {
     if (mpx_mma_eligible(pl, k)) return mpx_mma_scratch_bytes(pl, k);
+    if (mpx_tmma_eligible(pl, k)) return mpx_tmma_scratch_bytes(pl, k);
     return (size_t)pl->prog.n_chunks * MPX_COEF_CAP * (size_t)k * sizeof(double);
 }

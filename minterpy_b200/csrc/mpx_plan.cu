@@ -191,6 +191,106 @@ int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_
     return MPX_OK;
 }
 
+// ---------------------------------------------------------------------------------------
+// Tile program for the tensor-core tree kernel (format: mpx_common.h).  Complete, sorted sets
+// only: inside a group (rows that agree in dimensions 2..) the leaves have dimension-1
+// exponents 0, 1, 2, .. and every leaf is a gap-free run e0 = 0..len-1.
+// ---------------------------------------------------------------------------------------
+void compile_tile_program(const int64_t *e, int64_t N, int m, TileProgram &tp)
+{
+    struct Leaf { int64_t first; int len; int group; };
+    std::vector<Leaf> leaves;
+    std::vector<int> group_end;    // index one past the last leaf of every group
+    for (int64_t s = 0; s < N;) {
+        int64_t t = s + 1;
+        while (t < N) {
+            bool same = true;
+            for (int i = 1; i < m; ++i) same = same && (e[t * m + i] == e[s * m + i]);
+            if (!same) break;
+            ++t;
+        }
+        bool new_group = leaves.empty();
+        if (!leaves.empty())
+            for (int i = 2; i < m; ++i) new_group = new_group || (e[s * m + i] != e[leaves.back().first * m + i]);
+        if (new_group && !leaves.empty()) group_end.push_back((int)leaves.size());
+        leaves.push_back({s, (int)(t - s), (int)group_end.size()});
+        s = t;
+    }
+    group_end.push_back((int)leaves.size());
+    const int U = std::max(m - 2, 0);
+    int max0 = 0;
+    for (int64_t j = 0; j < N; ++j) max0 = std::max<int>(max0, (int)e[j * m]);
+    tp.ks_max = (max0 + 1 + 3) / 4;
+    tp.desc.clear();
+    tp.slot_src.assign(MPX_T_COEF_CAP, -1);
+    tp.n_chunks = 0;
+    tp.n_tiles = 0;
+    tp.mma_fma_per_point = tp.fma_per_point = 0;
+    std::vector<uint32_t> words;
+    int coef_used = 0;
+    auto flush = [&]() {
+        size_t base = tp.desc.size();
+        tp.desc.resize(base + MPX_T_DESC_WORDS, 0u);
+        tp.desc[base] = (uint32_t)words.size();
+        std::copy(words.begin(), words.end(), tp.desc.begin() + base + MPX_DESC_HDR);
+        tp.n_chunks++;
+        tp.slot_src.resize((size_t)(tp.n_chunks + 1) * MPX_T_COEF_CAP, -1);
+        words.clear();
+        coef_used = 0;
+    };
+    const int L = (int)leaves.size();
+    for (int i = 0; i < L;) {
+        const int g = leaves[i].group;
+        const int gend = group_end[g];
+        const int ncur = std::min(8, gend - i);
+        const bool ends = (i + ncur == gend);
+        int nnext = 0;
+        if (ends && ncur < 8 && gend < L) {
+            // head of the next group, but never its last leaf (one group end per tile)
+            const int next_size = group_end[g + 1] - gend;
+            nnext = std::min(8 - ncur, next_size - 1);
+        }
+        int maxlen = 0;
+        for (int c = 0; c < ncur + nnext; ++c) maxlen = std::max(maxlen, leaves[i + c].len);
+        const int ks = (maxlen + 3) / 4;
+        const bool last = ends && gend == L;
+        const int64_t *cur = e + leaves[i].first * m;
+        int nf = 0, adv_exp = 0;
+        if (ends) {
+            if (last) {
+                nf = U;
+            } else {
+                const int64_t *nxt = e + leaves[gend].first * m;
+                int D = 2;
+                for (int d = m - 1; d >= 2; --d) if (nxt[d] != cur[d]) { D = d; break; }
+                nf = D - 1;
+                adv_exp = (int)cur[D];
+            }
+        }
+        if (coef_used + ks * 32 > MPX_T_COEF_CAP ||
+            (int)words.size() + 2 > MPX_T_DESC_WORDS - MPX_DESC_HDR)
+            flush();
+        int32_t *slots = tp.slot_src.data() + (size_t)tp.n_chunks * MPX_T_COEF_CAP + coef_used;
+        for (int c = 0; c < ncur + nnext; ++c) {
+            const Leaf &lf = leaves[i + c];
+            for (int e0 = 0; e0 < lf.len; ++e0)
+                slots[(e0 >> 2) * 32 + c * 4 + (e0 & 3)] = (int32_t)(lf.first + e0);
+        }
+        coef_used += ks * 32;
+        const int e1 = (m >= 2) ? (int)cur[1] : 0;
+        words.push_back((uint32_t)ks | ((uint32_t)ncur << 5) | ((uint32_t)nnext << 9) |
+                        ((uint32_t)e1 << 13) | ((uint32_t)ends << 21) | ((uint32_t)nf << 22) |
+                        ((uint32_t)last << 26));
+        words.push_back((uint32_t)adv_exp);
+        tp.n_tiles++;
+        tp.mma_fma_per_point += 32 * ks;
+        tp.fma_per_point += 32 * ks + 8 + (ends ? nf : 0);
+        i += ncur + nnext;
+    }
+    flush();
+    tp.slot_src.resize((size_t)tp.n_chunks * MPX_T_COEF_CAP);
+}
+
 template <class T>
 int upload(T **dst, const std::vector<T> &src)
 {
@@ -415,6 +515,16 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
         rc = compile_program(e, N, m, order, mpx_l0p_for(pl->max_exp[0]), pl->prog, err);
         if (rc != MPX_OK) return mpx_fail(rc, err);
     }
+    if (complete && m >= 2 && m <= 8 && pl->max_exp[0] + 1 <= 68 && !getenv("MPX_NO_TMMA")) {
+        compile_tile_program(e, N, m, pl->tprog);
+        // Worth it only if the zero padding of the tiles stays small: measured on the B200 the
+        // tensor-core kernel wins when it executes at most ~12 % more FMAs than the DFMA tree
+        // kernel (full grids, long leaves: cfg5 +22 %), and loses beyond (cfg2: 27 % more FMAs).
+        // MPX_FORCE_TMMA=1 takes it whenever it was built (tests, experiments).
+        const int64_t tree_fma = pl->tree_ok ? pl->prog.fma_per_point : 0;
+        pl->tprog.usable = getenv("MPX_FORCE_TMMA") != nullptr || !pl->tree_ok ||
+                           100 * pl->tprog.fma_per_point <= 112 * tree_fma;
+    }
     // upper-level exponents of the first leaf (0 for every downward-closed set)
     for (int i = 2; i < m; ++i) {
         pl->start_exp[i] = (int)e[order[0] * m + i];
@@ -428,6 +538,10 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
 
     if ((rc = upload(&pl->d_desc, pl->prog.desc)) != MPX_OK) return rc;
     if ((rc = upload(&pl->d_slot_src, pl->prog.slot_src)) != MPX_OK) return rc;
+    if (pl->tprog.usable) {
+        if ((rc = upload(&pl->d_tdesc, pl->tprog.desc)) != MPX_OK) return rc;
+        if ((rc = upload(&pl->d_tslot_src, pl->tprog.slot_src)) != MPX_OK) return rc;
+    }
     std::vector<double> gpt((size_t)m * pl->gp_rows);
     for (int i = 0; i < m; ++i)
         for (int j = 0; j < pl->gp_rows; ++j) gpt[(size_t)i * pl->gp_rows + j] = gp_h[(size_t)j * m + i];
@@ -495,6 +609,8 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
     DeviceGuard dg(pl->device);
     cudaFree(pl->d_desc);
     cudaFree(pl->d_slot_src);
+    cudaFree(pl->d_tdesc);
+    cudaFree(pl->d_tslot_src);
     cudaFree(pl->d_gp);
     cudaFree(pl->d_exp8);
     cudaFree(pl->d_max_exp);
@@ -541,6 +657,10 @@ extern "C" int mpx_plan_info(const mpx_plan *pl, int what, int64_t *value_out)
     case MPX_INFO_DEVICE: *value_out = pl->device; break;
     case MPX_INFO_SCRATCH_BYTES: *value_out = (int64_t)pl->scratch_bytes; break;
     case MPX_INFO_CHUNKS: *value_out = pl->prog.n_chunks; break;
+    case MPX_INFO_SMALLK_KERNEL:
+        *value_out = mpx_tmma_eligible(pl, 1) ? 1 : (pl->tree_ok ? 0 : 2);
+        break;
+    case MPX_INFO_TMMA_FMA: *value_out = pl->tprog.fma_per_point; break;
     default: return mpx_fail(MPX_ERR_ARG, "unknown info key");
     }
     return MPX_OK;
@@ -581,5 +701,19 @@ extern "C" int mpx_debug_program(const int64_t *exponents_h, int64_t N, int m, u
     if (fma_out) *fma_out = pg.fma_per_point;
     if (desc_out) std::copy(pg.desc.begin(), pg.desc.end(), desc_out);
     if (slot_out) std::copy(pg.slot_src.begin(), pg.slot_src.end(), slot_out);
+    return MPX_OK;
+}
+
+// Host-only view of the tile program (tensor-core tree kernel), for the CPU tests.
+extern "C" int mpx_debug_tile_program(const int64_t *exponents_h, int64_t N, int m, uint32_t *desc_out,
+                                      int32_t *slot_out, int64_t *n_chunks_out, int64_t *fma_out)
+{
+    if (!exponents_h || N < 1 || m < 2 || m > MPX_MAX_M) return mpx_fail(MPX_ERR_ARG, "bad argument");
+    TileProgram tp;
+    compile_tile_program(exponents_h, N, m, tp);
+    if (n_chunks_out) *n_chunks_out = tp.n_chunks;
+    if (fma_out) *fma_out = tp.fma_per_point;
+    if (desc_out) std::copy(tp.desc.begin(), tp.desc.end(), desc_out);
+    if (slot_out) std::copy(tp.slot_src.begin(), tp.slot_src.end(), slot_out);
     return MPX_OK;
 }

@@ -347,3 +347,26 @@ def test_long_higher_dimensions(mpb):
         c = rng.uniform(-1, 1, (e.shape[0], k)) * 1e-3
         got = mpb.Plan(e, gp).eval(xx, c)
         assert rel_err(got, oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL
+
+
+@pytest.mark.parametrize("force", ["MPX_FORCE_TMMA", "MPX_NO_TMMA"])
+def test_both_tree_kernels(mpb, golden_small, golden_cfg, monkeypatch, force):
+    """Complete index sets with few polynomials can run on the DFMA tree kernel (mpx_eval.cu) or
+    on the tensor-core tree kernel (mpx_eval_tmma.cu); the plan picks by padding overhead.  Both
+    are forced here (the variable is read when the plan is built) on every golden shape."""
+    monkeypatch.setenv(force, "1")
+    for tag in SMALL_TAGS:
+        e, gp, xx = golden_small[f"{tag}/exponents"], golden_small[f"{tag}/generating_points"], golden_small[f"{tag}/xx"]
+        plan = mpb.Plan(e, gp)
+        for k in (1, 10):
+            c = golden_small[f"{tag}/k{k}/coeffs"][:, :5]          # k < 8: one of the tree kernels
+            ref = golden_small[f"{tag}/k{k}/eval_ref"][:, :5]
+            assert rel_err(plan.eval(xx, c), ref) <= EVAL_RTOL
+    for tag in ("cfg1", "cfg2", "cfg4", "cfg5"):
+        g = golden_cfg(tag)
+        e, gp = g["exponents"], g["generating_points"]
+        rng = np.random.default_rng(4)
+        c = rng.uniform(-1, 1, (e.shape[0], 2))
+        xx = np.concatenate([g["xx"][:300], -np.ones((1, e.shape[1])), np.ones((1, e.shape[1]))])
+        got = mpb.Plan(e, gp).eval(xx, c)
+        assert rel_err(got, oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=4)) <= EVAL_RTOL

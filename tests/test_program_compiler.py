@@ -62,3 +62,32 @@ def test_duplicate_rows_and_many_chunks():
     desc, _, _ = compile_program(e)
     assert desc.shape[0] >= 2
     _check(e, gp, n_points=1)
+
+
+# ---- tile program (tensor-core tree kernel) -------------------------------------------------
+from program_interp import compile_tile_program, run_tile_program  # noqa: E402
+
+
+def _check_tiles(e, gp, n_points=2, seed=0):
+    rng = np.random.default_rng(seed)
+    N, m = e.shape
+    coeffs = rng.uniform(-1, 1, N)
+    xx = rng.uniform(-1, 1, (n_points, m))
+    desc, slots, fma = compile_tile_program(e)
+    ref = oracle.eval_newton_polynomials(xx, coeffs, e, gp).reshape(-1)
+    for p in range(n_points):
+        val, fma_run = run_tile_program(desc, slots, xx[p], coeffs, e, gp)
+        assert abs(val - ref[p]) <= 1e-12 * max(1.0, np.max(np.abs(ref)))
+        assert fma_run == fma
+    return fma
+
+
+@pytest.mark.parametrize("tag", [t for t in SMALL_TAGS if not t.startswith("m1_")])
+def test_tile_program_small_sets(golden_small, tag):
+    _check_tiles(golden_small[f"{tag}/exponents"], golden_small[f"{tag}/generating_points"])
+
+
+@pytest.mark.parametrize("tag", ["cfg2", "cfg3", "cfg4", "cfg5"])
+def test_tile_program_config_sets(golden_cfg, tag):
+    g = golden_cfg(tag)
+    _check_tiles(g["exponents"], g["generating_points"], n_points=1)
