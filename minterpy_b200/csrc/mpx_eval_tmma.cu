@@ -71,13 +71,16 @@ __device__ __forceinline__ double quad_sum(double v)
 // shared memory (dynamic): [0,128) mbarriers | ring T_STAGES x T_STAGE_BYTES | gp (m x gp_rows)
 // | T1 [(max_exp1+2)][PS] (last row zero) | x of dimensions 2.. [U][PS] | running product and partial sum of
 // dimensions 3.. [2][U-1][PS];  PS = points + 2 (bank spread of the T1 rows)
-template <int KS0, int NW, int MINB>
+// MT = 8-point m-tiles per warp (4: fewest issues per FMA; 2: half the A-fragment registers,
+// more resident warps)
+template <int KS0, int NW, int MT, int MINB>
 __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaParams p)
 {
     constexpr int NTH = 32 * NW;
+    constexpr int PTS = NW * 8 * MT;          // points per CTA
     // row stride of the point-indexed tables: PS*2 words = 4 (mod 32), so the rows e1 + 2*jl + h
     // read by the four lane groups of a half-warp fall on disjoint banks
-    constexpr int PS = NTH + 2;
+    constexpr int PS = PTS + 2;
     extern __shared__ __align__(128) unsigned char smem[];
     uint64_t *full = reinterpret_cast<uint64_t *>(smem);
     uint64_t *empty = full + T_STAGES;
@@ -122,8 +125,8 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
     }
 
     // ---- per-point tables: thread = point for the shared-memory ones ----------------------
-    const int64_t p0 = (int64_t)blockIdx.x * NTH;
-    {
+    const int64_t p0 = (int64_t)blockIdx.x * PTS;
+    if (tid < PTS) {
         int64_t pt = p0 + tid;
         if (pt >= p.P) pt = p.P - 1;
         const double *xp = p.xx + pt * p.ld_xx;
@@ -144,11 +147,11 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
         }
     }
     // A fragments: T0[point 8*mt + g of this warp][e0 = 4*s + jl]
-    double a[KS0][4];
-    int64_t ptq[4];
+    double a[KS0][MT];
+    int64_t ptq[MT];
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt) {
-        int64_t pt = p0 + warp * 32 + mt * 8 + g;
+    for (int mt = 0; mt < MT; ++mt) {
+        int64_t pt = p0 + warp * (8 * MT) + mt * 8 + g;
         ptq[mt] = pt;
         if (pt >= p.P) pt = p.P - 1;
         const double x0 = p.xx[pt * p.ld_xx];
@@ -162,12 +165,12 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
     }
     __syncthreads();
 
-    const int pbase = warp * 32 + g;                 // shared-memory column of m-tile 0; +8 per tile
-    double acc_cur[4], t2[4], a2[4];
+    const int pbase = warp * (8 * MT) + g;                 // shared-memory column of m-tile 0; +8 per tile
+    double acc_cur[MT], t2[MT], a2[MT];
     const uint32_t t1_lane = smem_u32(T1s + pbase);      // T1[0][point of m-tile 0]; +64 B per tile
     const uint32_t zrow = (uint32_t)(me1 + 1);
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt) {
+    for (int mt = 0; mt < MT; ++mt) {
         acc_cur[mt] = 0.0;
         t2[mt] = 1.0;
         a2[mt] = 0.0;
@@ -204,15 +207,15 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
             const int ks = w0 & 31;
             const int ncur = (w0 >> 5) & 15, nnext = (w0 >> 9) & 15;
             const int e1 = (w0 >> 13) & 255;
-            double cacc[4][2];
+            double cacc[MT][2];
 #pragma unroll
-            for (int mt = 0; mt < 4; ++mt) cacc[mt][0] = cacc[mt][1] = 0.0;
+            for (int mt = 0; mt < MT; ++mt) cacc[mt][0] = cacc[mt][1] = 0.0;
 #pragma unroll
             for (int st = 0; st < KS0; ++st) {
                 if (st < ks) {
                     const double b = lds64(cf + 256 * st);
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) dmma884(cacc[mt][0], cacc[mt][1], a[st][mt], b);
+                    for (int mt = 0; mt < MT; ++mt) dmma884(cacc[mt][0], cacc[mt][1], a[st][mt], b);
                 }
             }
             cf += 256u * ks;
@@ -224,30 +227,30 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
                 const uint32_t row = col < ncur ? (uint32_t)(e1 + col) : zrow;
                 const uint32_t ta = t1_lane + row * (uint32_t)(PS * 8);
 #pragma unroll
-                for (int mt = 0; mt < 4; ++mt)
+                for (int mt = 0; mt < MT; ++mt)
                     acc_cur[mt] = fma(lds64(ta + 64 * mt), cacc[mt][h], acc_cur[mt]);
             }
             if (w0 & (1u << 21)) {
                 // the current group ends: sum over the 4 lanes of a point, fold upwards
                 const int nf = (w0 >> 22) & 15;
                 const bool last = (w0 >> 26) & 1u;
-                double low[4];
+                double low[MT];
 #pragma unroll
-                for (int mt = 0; mt < 4; ++mt) low[mt] = quad_sum(acc_cur[mt]);
+                for (int mt = 0; mt < MT; ++mt) low[mt] = quad_sum(acc_cur[mt]);
                 if (nf == 0) {
                     // m == 2: single group, the program is over
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) a2[mt] = low[mt];
+                    for (int mt = 0; mt < MT; ++mt) a2[mt] = low[mt];
                 } else if (nf == 1) {
                     const double g2 = gps[2 * p.gp_rows + (int)w1];
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) {
+                    for (int mt = 0; mt < MT; ++mt) {
                         a2[mt] = fma(t2[mt], low[mt], a2[mt]);
                         if (!last) t2[mt] *= xs[pbase + 8 * mt] - g2;
                     }
                 } else {
 #pragma unroll
-                    for (int mt = 0; mt < 4; ++mt) {
+                    for (int mt = 0; mt < MT; ++mt) {
                         low[mt] = fma(t2[mt], low[mt], a2[mt]);
                         a2[mt] = 0.0;
                         t2[mt] = 1.0;
@@ -258,7 +261,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
                         const bool top = (u == nf - 1);
                         const double gu = gps[(2 + u) * p.gp_rows + (int)w1];
 #pragma unroll
-                        for (int mt = 0; mt < 4; ++mt) {
+                        for (int mt = 0; mt < MT; ++mt) {
                             // the 4 lanes of a point compute and store identical values
                             const double tv = ut[8 * mt];
                             const double av = fma(tv, low[mt], ut[up_stride + 8 * mt]);
@@ -275,7 +278,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
                     }
                 }
 #pragma unroll
-                for (int mt = 0; mt < 4; ++mt) acc_cur[mt] = 0.0;
+                for (int mt = 0; mt < MT; ++mt) acc_cur[mt] = 0.0;
                 if (nnext) {
                     // head of the next group in the same tile: its dimension-1 exponents start at 0
 #pragma unroll
@@ -284,7 +287,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
                         const uint32_t row = (col >= ncur && col < ncur + nnext) ? (uint32_t)(col - ncur) : zrow;
                         const uint32_t ta = t1_lane + row * (uint32_t)(PS * 8);
 #pragma unroll
-                        for (int mt = 0; mt < 4; ++mt)
+                        for (int mt = 0; mt < MT; ++mt)
                             acc_cur[mt] = fma(lds64(ta + 64 * mt), cacc[mt][h], acc_cur[mt]);
                     }
                 }
@@ -296,7 +299,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
     // ---- result: every point is held by 4 lanes, lane jl == 0 writes ---------------------------
     if (jl == 0) {
 #pragma unroll
-        for (int mt = 0; mt < 4; ++mt) {
+        for (int mt = 0; mt < MT; ++mt) {
             if (ptq[mt] < p.P) {
                 const double res = (U <= 1) ? a2[mt] : ups[up_stride + (size_t)(U - 2) * PS + pbase + 8 * mt];
                 p.out[ptq[mt] * p.ld_out + q] = res;
@@ -305,12 +308,12 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
     }
 }
 
-template <int KS0, int NW, int MINB>
+template <int KS0, int NW, int MT, int MINB>
 int launch_tmma(const TmmaParams &prm, int k, size_t smem, cudaStream_t stream)
 {
-    auto fn = &eval_tmma_kernel<KS0, NW, MINB>;
+    auto fn = &eval_tmma_kernel<KS0, NW, MT, MINB>;
     MPX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t ptiles = (prm.P + 32 * NW - 1) / (32 * NW);
+    const int64_t ptiles = (prm.P + 8 * MT * NW - 1) / (8 * MT * NW);
     if (ptiles > 0x7fffffffLL || k > 65535)
         return mpx_fail(MPX_ERR_UNSUPPORTED, "too many points or polynomials for one launch");
     fn<<<dim3((unsigned)ptiles, (unsigned)k, 1), 32 * NW, smem, stream>>>(prm);
@@ -318,9 +321,9 @@ int launch_tmma(const TmmaParams &prm, int k, size_t smem, cudaStream_t stream)
     return MPX_OK;
 }
 
-size_t tmma_smem_bytes(const mpx_plan *pl, int nw)
+size_t tmma_smem_bytes(const mpx_plan *pl, int pts)
 {
-    const int ps = 32 * nw + 2;
+    const int ps = pts + 2;
     const int U = pl->m - 2;
     size_t doubles = (size_t)((pl->m * pl->gp_rows + 1) & ~1) + (size_t)(pl->max_exp[1] + 2) * ps +
                      (size_t)(U > 0 ? U : 0) * ps + (size_t)2 * (U > 1 ? U - 1 : 0) * ps;
@@ -332,7 +335,7 @@ size_t tmma_smem_bytes(const mpx_plan *pl, int nw)
 bool mpx_tmma_eligible(const mpx_plan *pl, int k)
 {
     (void)k;
-    return pl->tprog.usable && pl->d_tdesc != nullptr && tmma_smem_bytes(pl, 8) <= (size_t)227 * 1024;
+    return pl->tprog.usable && pl->d_tdesc != nullptr && tmma_smem_bytes(pl, 256) <= (size_t)227 * 1024;
 }
 
 size_t mpx_tmma_scratch_bytes(const mpx_plan *pl, int k)
@@ -359,13 +362,20 @@ int mpx_launch_eval_tmma(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_x
     prm.desc = pl->d_tdesc; prm.coef = pl->d_scratch; prm.gp = pl->d_gp;
     prm.n_chunks = pl->tprog.n_chunks; prm.m = pl->m; prm.gp_rows = pl->gp_rows;
     for (int i = 0; i < 8; ++i) prm.max_exp[i] = i < pl->m ? pl->max_exp[i] : 0;
-    const size_t smem = tmma_smem_bytes(pl, 8);
     const int ks = pl->tprog.ks_max;
-    if (ks <= 3) return launch_tmma<3, 8, 2>(prm, k, smem, stream);
-    if (ks <= 5) return launch_tmma<5, 8, 2>(prm, k, smem, stream);
-    static const bool one_cta /* two CTAs when set */ = getenv("MPX_TMMA_TWO_CTA") != nullptr;     // experiment knob
-    if (ks <= 9) return one_cta ? launch_tmma<9, 8, 2>(prm, k, smem, stream)
-                                : launch_tmma<9, 8, 1>(prm, k, smem, stream);
-    if (ks <= 17) return launch_tmma<17, 8, 1>(prm, k, smem, stream);
+    static const int env_mt = getenv("MPX_TMMA_MT") ? atoi(getenv("MPX_TMMA_MT")) : 0;   // experiment knob
+    const bool mt2 = env_mt ? env_mt == 2 : ks > 5;
+    const size_t smem = tmma_smem_bytes(pl, mt2 ? 128 : 256);
+    if (mt2) {
+        if (ks <= 3) return launch_tmma<3, 8, 2, 3>(prm, k, smem, stream);
+        if (ks <= 5) return launch_tmma<5, 8, 2, 3>(prm, k, smem, stream);
+        if (ks <= 9) return launch_tmma<9, 8, 2, 2>(prm, k, smem, stream);
+        if (ks <= 17) return launch_tmma<17, 8, 2, 1>(prm, k, smem, stream);
+    } else {
+        if (ks <= 3) return launch_tmma<3, 8, 4, 2>(prm, k, smem, stream);
+        if (ks <= 5) return launch_tmma<5, 8, 4, 2>(prm, k, smem, stream);
+        if (ks <= 9) return launch_tmma<9, 8, 4, 1>(prm, k, smem, stream);
+        if (ks <= 17) return launch_tmma<17, 8, 4, 1>(prm, k, smem, stream);
+    }
     return mpx_fail(MPX_ERR_UNSUPPORTED, "dimension-0 table too long for the tensor-core tree kernel");
 }
