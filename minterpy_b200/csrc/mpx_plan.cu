@@ -517,13 +517,14 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
     }
     if (complete && m >= 2 && m <= 8 && pl->max_exp[0] + 1 <= 68 && !getenv("MPX_NO_TMMA")) {
         compile_tile_program(e, N, m, pl->tprog);
-        // Worth it only if the zero padding of the tiles stays small: measured on the B200 the
-        // tensor-core kernel wins when it executes at most ~12 % more FMAs than the DFMA tree
-        // kernel (full grids, long leaves: cfg5 +22 %), and loses beyond (cfg2: 27 % more FMAs).
-        // MPX_FORCE_TMMA=1 takes it whenever it was built (tests, experiments).
+        // Worth it only for long dimension-0 tables (more than 5 k-steps, n > 19) whose tiles
+        // carry almost no zero padding -- in practice full tensor grids (lp = inf).  Measured
+        // on the B200: cfg5 (6 % more FMAs than the DFMA tree kernel) 1.17e13 vs 8.8e12 pm/s;
+        // m=3, n=24, lp=2 (21 % more) 5.5e12 vs 7.3e12; cfg2 (27 % more, short tiles) 6.8e12 vs
+        // 8.6e12.  MPX_FORCE_TMMA=1 takes it whenever it was built (tests, experiments).
         const int64_t tree_fma = pl->tree_ok ? pl->prog.fma_per_point : 0;
         pl->tprog.usable = getenv("MPX_FORCE_TMMA") != nullptr || !pl->tree_ok ||
-                           100 * pl->tprog.fma_per_point <= 112 * tree_fma;
+                           (pl->tprog.ks_max > 5 && 100 * pl->tprog.fma_per_point <= 110 * tree_fma);
     }
     // upper-level exponents of the first leaf (0 for every downward-closed set)
     for (int i = 2; i < m; ++i) {

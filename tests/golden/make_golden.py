@@ -148,10 +148,23 @@ def config_case(tag):
     return out
 
 
+def extra_shapes():
+    """Index sets and grids only (no reference outputs): shapes between the BASELINE configs,
+    used by the GPU tests against the pinned oracle."""
+    out = {}
+    for (m, n, lp) in [(3, 24, 2.0), (2, 40, 1.0), (4, 20, 1.0)]:
+        mi, grid = shape_arrays(m, n, lp)
+        tag = f"m{m}_n{n}_lp{lp}"
+        out[f"{tag}/exponents"] = mi.exponents.astype(np.uint8)
+        out[f"{tag}/generating_points"] = grid.generating_points
+    return out
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["small"] + list(CONFIGS)
     for tag in which:
         path = os.path.join(HERE, f"{tag}.npz")
-        data = small_cases() if tag == "small" else config_case(tag)
+        data = (small_cases() if tag == "small" else extra_shapes() if tag == "shapes_extra"
+                else config_case(tag))
         np.savez_compressed(path, **data)
         print("wrote", path, os.path.getsize(path), flush=True)

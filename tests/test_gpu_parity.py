@@ -370,3 +370,20 @@ def test_both_tree_kernels(mpb, golden_small, golden_cfg, monkeypatch, force):
         xx = np.concatenate([g["xx"][:300], -np.ones((1, e.shape[1])), np.ones((1, e.shape[1]))])
         got = mpb.Plan(e, gp).eval(xx, c)
         assert rel_err(got, oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=4)) <= EVAL_RTOL
+
+
+def test_intermediate_shapes_against_oracle(mpb):
+    """Index sets between the BASELINE configs (from the reference, tests/golden/shapes_extra.npz):
+    long dimension-0 tables with staircase leaves -- the shapes where the plan switches between
+    the DFMA and the tensor-core tree kernel."""
+    g = golden_io.load("shapes_extra")
+    rng = np.random.default_rng(31)
+    for tag in ("m3_n24_lp2.0", "m2_n40_lp1.0", "m4_n20_lp1.0"):
+        e, gp = g[f"{tag}/exponents"], g[f"{tag}/generating_points"]
+        plan = mpb.Plan(e, gp)
+        for k in (1, 3):
+            c = rng.uniform(-1, 1, (e.shape[0], k))
+            xx = rng.uniform(-1, 1, (257, e.shape[1]))
+            assert rel_err(plan.eval(xx, c), oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=4)) <= EVAL_RTOL
+        v = rng.uniform(-1, 1, (e.shape[0], 2))
+        assert np.array_equal(plan.dds(v), oracle.dds(v, e, gp))
