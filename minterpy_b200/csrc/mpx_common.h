@@ -40,7 +40,7 @@ constexpr uint32_t MPX_D_LAST = 1u << 13;
 inline int mpx_l0p_for(int max_exp0)
 {
     const int L0 = max_exp0 + 1;
-    return L0 <= 10 ? 10 : L0 <= 18 ? 18 : L0 <= 34 ? 34 : 66;
+    return L0 <= 10 ? 10 : L0 <= 18 ? 18 : L0 <= 26 ? 26 : L0 <= 34 ? 34 : 66;
 }
 inline int mpx_count_words(int l0p) { return (l0p / 2 + 7) / 8; }
 

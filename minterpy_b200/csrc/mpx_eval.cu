@@ -138,6 +138,13 @@ struct LengthChain {
                                               uint32_t &cp, uint32_t &t1a,
                                               const uint32_t (&counts)[(L0P / 2 + 7) / 8])
     {
+        // entering a count word (8 lengths) that is all zero: skip its lengths in one test
+        constexpr bool word_top = ((K - 1) % 8 == 7) || (K == L0P / 2);
+        constexpr int below = ((K - 1) / 8) * 8;         // first length of the next lower word
+        if (word_top && counts[(K - 1) / 8] == 0u) {
+            if constexpr (below >= 1) LengthChain<L0P, R, A, NT, (below >= 1 ? below : 1)>::go(acc1, T0, cp, t1a, counts);
+            return;
+        }
         const int cnt = (int)((counts[(K - 1) / 8] >> (4 * ((K - 1) % 8))) & 15u);
         if (cnt) run_leaves<L0P, R, A, NT, K>(acc1, T0, cp, t1a, cnt);
         if constexpr (K > 1) LengthChain<L0P, R, A, NT, K - 1>::go(acc1, T0, cp, t1a, counts);
@@ -462,6 +469,10 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
         {18, 4, 128, kfn<18, 4, 1, 128, 1>()},
         {18, 4, 64, kfn<18, 4, 1, 64, 1>()},
         {18, 1, 64, kfn<18, 1, 2, 64, 1>()},
+        {26, 3, 256, kfn<26, 3, 1, 256, 1>()},
+        {26, 3, 128, kfn<26, 3, 1, 128, 1>()},
+        {26, 3, 64, kfn<26, 3, 1, 64, 1>()},
+        {26, 1, 64, kfn<26, 1, 2, 64, 1>()},
         {34, 2, 256, kfn<34, 2, 2, 256, 1>()},
         {34, 2, 128, kfn<34, 2, 2, 128, 1>()},
         {34, 2, 64, kfn<34, 2, 2, 64, 1>()},
@@ -470,11 +481,11 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
         {66, 1, 128, kfn<66, 1, 2, 128, 1>()},
         {66, 1, 64, kfn<66, 1, 2, 64, 1>()},
         // experimental alternatives, selected with MPX_EVAL_VARIANT=<index>
-        {18, 4, 256, kfn<18, 4, 2, 256, 1>()},   // 15: two accumulators per point
-        {18, 3, 384, kfn<18, 3, 1, 384, 1>()},   // 16: 3 points, 12 warps
-        {18, 2, 512, kfn<18, 2, 1, 512, 1>()},   // 17: 2 points, 16 warps in one CTA
+        {18, 4, 256, kfn<18, 4, 2, 256, 1>()},   // 19: two accumulators per point
+        {18, 3, 384, kfn<18, 3, 1, 384, 1>()},   // 20: 3 points, 12 warps
+        {18, 2, 512, kfn<18, 2, 1, 512, 1>()},   // 21: 2 points, 16 warps in one CTA
     };
-    constexpr int n_standard = 15;
+    constexpr int n_standard = 19;
     int smem_max = 0;
     MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
     // tuning knobs for experiments (defaults are what the library ships with)

@@ -31,7 +31,7 @@ def compile_program(exponents):
 
 def l0p_for(max_exp0):
     L0 = max_exp0 + 1
-    return 10 if L0 <= 10 else 18 if L0 <= 18 else 34 if L0 <= 34 else 66
+    return 10 if L0 <= 10 else 18 if L0 <= 18 else 26 if L0 <= 26 else 34 if L0 <= 34 else 66
 
 
 def run_program(desc, slots, x, coeffs, exponents, gp):
