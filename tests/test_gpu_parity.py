@@ -387,3 +387,25 @@ def test_intermediate_shapes_against_oracle(mpb):
             assert rel_err(plan.eval(xx, c), oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=4)) <= EVAL_RTOL
         v = rng.uniform(-1, 1, (e.shape[0], 2))
         assert np.array_equal(plan.dds(v), oracle.dds(v, e, gp))
+
+
+@pytest.mark.parametrize("tag,P,k", [("cfg5", 1 << 20, 1), ("cfg3", 1 << 17, 64), ("cfg4", 1 << 15, 256)])
+def test_large_properties_other_configs(mpb, golden_cfg, tag, P, k):
+    """BASELINE configs 3-5 at sizes the oracle cannot reach in seconds (tensor-core tree kernel,
+    DMMA contraction kernel): linearity in the coefficients and an oracle spot check."""
+    import torch
+    g = golden_cfg(tag)
+    e, gp = g["exponents"], g["generating_points"]
+    N, m = e.shape
+    plan = mpb.get_plan(e, gp)
+    gen = torch.Generator(device="cuda").manual_seed(5 + k)
+    xx = torch.rand((P, m), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+    c1 = torch.rand((N, k), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+    c2 = torch.rand((N, k), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+    y1, y2 = plan.eval(xx, c1), plan.eval(xx, c2)
+    y12 = plan.eval(xx, c1 - 0.25 * c2)
+    scale = max(y1.abs().max().item(), y2.abs().max().item())
+    assert (y12 - (y1 - 0.25 * y2)).abs().max().item() <= 1e-12 * scale
+    idx = torch.randint(0, P, (24,), generator=gen, device="cuda")
+    ref = oracle.eval_newton_polynomials(xx[idx].cpu().numpy(), c1.cpu().numpy(), e, gp, nthreads=4)
+    assert rel_err(y1[idx].cpu().numpy(), ref) <= EVAL_RTOL
