@@ -142,9 +142,15 @@ def cpu_baseline(e, gp, k, target_seconds=12.0, seed=1):
     t = time.perf_counter()
     oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=cores)
     dt = time.perf_counter() - t
+    # the reference's Numba stage is single-threaded: also time one thread on a 3 s sample
+    P1 = int(max(64, min(rate / cores * 3.0, P)))
+    t = time.perf_counter()
+    oracle.eval_newton_polynomials(xx[:P1], c, e, gp, nthreads=1)
+    dt1 = time.perf_counter() - t
     return {"value": P * N / dt, "unit": "point*monomials/s", "cores": cores, "kind": "port",
             "sample": f"{P} points of the workload ({dt:.1f} s), oracle/newton_oracle.c on "
-                      f"{cores} threads", "seconds": dt, "points": P}
+                      f"{cores} threads", "single_core_value": P1 * N / dt1,
+            "seconds": dt, "points": P}
 
 
 def run_reference(args):
