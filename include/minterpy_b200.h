@@ -158,6 +158,36 @@ int mpx_apply_dense(int device, const double *T, int64_t rows, int64_t cols, int
                     const double *c, int k, int64_t ld_c, double *out, int64_t ld_out,
                     void *stream);
 
+/*
+ * Evaluate a partial derivative of k polynomials in Newton form at P points.
+ *   replaces: deriv_newt_eval(x, coefficients, exponents, generating_points,
+ *             derivative_order_along)  src/minterpy/polynomials/utils.py:8-112, the evaluation
+ *             behind NewtonPolynomial.diff / partial_diff
+ *             (src/minterpy/polynomials/newton_polynomial.py:55-86).
+ * orders_h: m derivative orders (host, >= 0); all zero is mpx_eval.  Other arguments as
+ * mpx_eval; unlike the reference, k > 1 coefficient columns are accepted.  The derivative of a
+ * product table entry prod_{t<q}(x - g_t) is formed by the product-rule recurrence (O(q * order)
+ * flops) instead of the reference's sum over itertools.combinations, so values agree up to
+ * rounding, not bit for bit.  MPX_ERR_UNSUPPORTED when m > 8 or the per-point tables of the
+ * index set do not fit shared memory.
+ */
+int mpx_eval_deriv(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+                   const double *coeffs, int k, int64_t ld_c, const int32_t *orders_h,
+                   double *out, int64_t ld_out, void *stream);
+
+/*
+ * Index-set predicates on a host exponent matrix (N x m, int64, row-major); no device work.
+ *   mpx_index_is_sorted:   rows strictly increasing in the reference's lexicographic order
+ *                          (last column most significant), i.e. sorted and duplicate-free.
+ *   mpx_index_is_complete: replaces is_lexicographically_complete
+ *                          src/minterpy/core/utils.py:234-262 (MultiIndexSet.is_complete,
+ *                          src/minterpy/core/multi_index.py:120-131): every index that is one
+ *                          smaller in one component is in the set.  O(N m^2) instead of the
+ *                          reference's O(N^2 m).  Unsorted input is MPX_ERR_ARG.
+ */
+int mpx_index_is_sorted(const int64_t *exponents_h, int64_t N, int m, int *sorted_out);
+int mpx_index_is_complete(const int64_t *exponents_h, int64_t N, int m, int *complete_out);
+
 #ifdef __cplusplus
 }
 #endif

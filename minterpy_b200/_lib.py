@@ -28,6 +28,10 @@ SIGNATURES = {
     "mpx_dds_host": (c_int, [c_vp, c_vp, c_int, c_i64, c_vp, c_i64]),
     "mpx_apply_dense": (c_int, [c_int, c_vp, c_i64, c_i64, c_i64, c_vp, c_int, c_i64, c_vp,
                                 c_i64, c_vp]),
+    "mpx_eval_deriv": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_int, c_i64, c_vp, c_vp, c_i64,
+                               c_vp]),
+    "mpx_index_is_sorted": (c_int, [c_vp, c_i64, c_int, ctypes.POINTER(c_int)]),
+    "mpx_index_is_complete": (c_int, [c_vp, c_i64, c_int, ctypes.POINTER(c_int)]),
 }
 # not part of the public header: host-only view of the compiled program, used by tests
 DEBUG_SIGNATURES = {

@@ -105,6 +105,31 @@ def eval_newton_polynomials(xx, coefficients, exponents, generating_points,
     return convert_eval_output(plan.eval(xx, coefficients))
 
 
+def deriv_newt_eval(x, coefficients, exponents, generating_points, derivative_order_along):
+    """Values of a partial derivative of polynomial(s) in Newton form
+    (``polynomials/utils.py:8-112``).  ``x`` (P, m); ``coefficients`` (N,) -> result (P,) as in
+    the reference, or (N, k) -> (P, k); ``derivative_order_along`` m non-negative ints."""
+    exponents = _as_host_int(exponents)
+    generating_points = _as_host_float(generating_points)
+    m = exponents.shape[1]
+    orders = np.asarray(derivative_order_along).reshape(-1)
+    if orders.shape[0] != m:
+        raise ValueError(f"derivative_order_along needs {m} entries, {orders.shape[0]} given")
+    if not np.issubdtype(orders.dtype, np.integer):
+        raise TypeError("derivative orders must be integers")
+    if (orders < 0).any():
+        raise ValueError("derivative orders must be non-negative")
+    if x.ndim != 2 or x.shape[1] != m:
+        raise ValueError(f"points of shape (P, {m}) expected, {tuple(x.shape)} given")
+    if coefficients.shape[0] != exponents.shape[0]:
+        raise ValueError(f"the coefficient amount {coefficients.shape[0]} does not match the "
+                         f"amount of monomials {exponents.shape[0]}")
+    one_d = coefficients.ndim == 1
+    c2 = coefficients.reshape(-1, 1) if one_d else coefficients
+    out = get_plan(exponents, generating_points).eval_deriv(x, c2, orders)
+    return out.reshape(-1) if one_d else out
+
+
 def eval_newton_monomials(x, exponents, generating_points, verify_input=False,
                           triangular=False):
     """The (points x monomials) matrix of Newton monomial values."""

@@ -27,6 +27,37 @@ extern "C" int mpx_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx
     return mpx_launch_eval(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, (cudaStream_t)stream);
 }
 
+extern "C" int mpx_eval_deriv(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
+                              const double *coeffs, int k, int64_t ld_c, const int32_t *orders_h,
+                              double *out, int64_t ld_out, void *stream)
+{
+    int rc = check_plan(pl);
+    if (rc) return rc;
+    if (!orders_h) return mpx_fail(MPX_ERR_ARG, "orders_h is null");
+    int orders[MPX_MAX_M];
+    bool any = false;
+    for (int i = 0; i < pl->m; ++i) {
+        if (orders_h[i] < 0) return mpx_fail(MPX_ERR_ARG, "derivative orders must be >= 0");
+        orders[i] = orders_h[i];
+        any = any || orders[i] > 0;
+    }
+    // order 0 everywhere is the polynomial itself (the reference builds the plain tables then)
+    if (!any) return mpx_eval(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
+    if (P < 0 || k < 1) return mpx_fail(MPX_ERR_ARG, "P must be >= 0 and k >= 1");
+    if (P == 0) return MPX_OK;
+    if (!xx || !coeffs || !out) return mpx_fail(MPX_ERR_ARG, "null device pointer");
+    if (ld_xx < pl->m || ld_c < k || ld_out < k) return mpx_fail(MPX_ERR_ARG, "leading dimension too small");
+    if (!mpx_mma_fits(pl, k))
+        return mpx_fail(MPX_ERR_UNSUPPORTED,
+                        "derivative evaluation runs on the shared-memory-table kernel: m <= 8 and "
+                        "m * (largest exponent + 1) * 68 doubles of tables must fit shared memory");
+    DeviceGuard dg(pl->device);
+    if (!dg.ok) return mpx_fail(MPX_ERR_CUDA, "cannot select the plan's CUDA device");
+    std::lock_guard<std::mutex> lock(pl->mu);
+    return mpx_launch_eval_mma(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, (cudaStream_t)stream,
+                               orders);
+}
+
 extern "C" int mpx_monomials(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
                              double *out, int64_t ld_out, int triangular, void *stream)
 {

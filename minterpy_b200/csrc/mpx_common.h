@@ -175,9 +175,11 @@ int mpx_ensure_scratch(mpx_plan *plan, size_t bytes);
 // tensor-core (many polynomials) evaluation path, mpx_eval_mma.cu
 bool mpx_mma_eligible(const mpx_plan *plan, int k);
 size_t mpx_mma_scratch_bytes(const mpx_plan *plan, int k);
+// orders_h (m entries, host) != nullptr: evaluate the partial derivative of those orders
 int mpx_launch_eval_mma(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
                         const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
-                        cudaStream_t stream);
+                        cudaStream_t stream, const int *orders_h = nullptr);
+bool mpx_mma_fits(const mpx_plan *plan, int k);   // the tables of this index set fit shared memory
 // tensor-core tree kernel (complete sets, few polynomials), mpx_eval_tmma.cu
 bool mpx_tmma_eligible(const mpx_plan *plan, int k);
 size_t mpx_tmma_scratch_bytes(const mpx_plan *plan, int k);

@@ -40,6 +40,7 @@ struct MmaParams {
     int gp_rows;
     int e1;                  // table entries per dimension (largest exponent + 1)
     int max_exp[8];
+    int order[8];            // derivative order per dimension (all 0: plain evaluation)
 };
 
 __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b)
@@ -64,6 +65,37 @@ __global__ void pack_mma_kernel(const double *__restrict__ coeffs, int64_t ld_c,
     const int c = (int)(r % rs);
     const int q = tile * 8 * nt8 + c;
     img[t] = (c < 8 * nt8 && q < k && j < N) ? coeffs[j * ld_c + q] : 0.0;
+}
+
+// Turns one column of product tables T[q] = prod_{t<q} (x - g_t) into its `order`-th derivative
+// with respect to x, in place (polynomials/utils.py:8-112 computes the same numbers as
+// order! * sum over all ways to drop `order` factors, itertools.combinations, at exponential
+// cost).  With F_j[q] = (d/dx)^j T[q] / j!, the product rule on T[q+1] = (x - g_q) T[q] gives
+//     F_j[q+1] = (x - g_q) F_j[q] + F_{j-1}[q],     F_j[0] = 0 for j >= 1,
+// so pass j rewrites the column from F_{j-1} to F_j walking q upwards (the old entry of row
+// q+1 is read just before it is overwritten).  Entries below `order` come out as exact zeros
+// and entry `order` as exactly order!, like the reference's table.
+template <int PS>
+__device__ __forceinline__ void derivative_table(double *T, double x, const double *g, int max_exp,
+                                                 int order)
+{
+    if (order > max_exp) {
+        for (int q = 0; q <= max_exp; ++q) T[(size_t)q * PS] = 0.0;
+        return;
+    }
+    for (int pass = 1; pass <= order; ++pass) {
+        double fj = 0.0, old = T[0];
+        T[0] = 0.0;
+        for (int q = 0; q < max_exp; ++q) {
+            const double old_next = T[(size_t)(q + 1) * PS];
+            fj = __fma_rn(x - g[q], fj, old);
+            T[(size_t)(q + 1) * PS] = fj;
+            old = old_next;
+        }
+    }
+    double fact = 1.0;
+    for (int t = 2; t <= order; ++t) fact *= (double)t;
+    for (int q = order; q <= max_exp; ++q) T[(size_t)q * PS] *= fact;
 }
 
 // MP = number of dimensions the monomial product is unrolled for (>= m; dimensions m..MP-1
@@ -132,6 +164,7 @@ __global__ void __launch_bounds__(32 * NW, 1) eval_mma_kernel(const MmaParams p)
                 T[(size_t)(j + 1) * PS] = prod;
             }
             for (int j = p.max_exp[i] + 1; j < E1; ++j) T[(size_t)j * PS] = 0.0;
+            if (p.order[i] > 0) derivative_table<PS>(T, x, gps + i * p.gp_rows, p.max_exp[i], p.order[i]);
         }
     }
     __syncthreads();
@@ -264,9 +297,15 @@ size_t mpx_mma_scratch_bytes(const mpx_plan *pl, int k)
     return (size_t)tiles * pl->mma_chunks * KC * (8 * nt8 + 4) * sizeof(double);
 }
 
+bool mpx_mma_fits(const mpx_plan *pl, int k)
+{
+    return pl->m <= 8 && pl->d_exp64 != nullptr &&
+           mma_smem_bytes(pl, mma_nt8_for(k), 2) <= MMA_SMEM_LIMIT;
+}
+
 int mpx_launch_eval_mma(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
                         const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
-                        cudaStream_t stream)
+                        cudaStream_t stream, const int *orders_h)
 {
     const int nt8 = mma_nt8_for(k);
     const int tiles = (k + 8 * nt8 - 1) / (8 * nt8);
@@ -288,6 +327,7 @@ int mpx_launch_eval_mma(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx
     int e1 = 1;
     for (int i = 0; i < pl->m; ++i) { prm.max_exp[i] = pl->max_exp[i]; e1 = std::max(e1, pl->max_exp[i] + 1); }
     for (int i = pl->m; i < 8; ++i) prm.max_exp[i] = 0;
+    for (int i = 0; i < 8; ++i) prm.order[i] = (orders_h && i < pl->m) ? orders_h[i] : 0;
     prm.e1 = e1;
 
     const int nw = mma_smem_bytes(pl, nt8, 8) <= MMA_SMEM_LIMIT ? 8 : 2;

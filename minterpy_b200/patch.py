@@ -4,12 +4,17 @@
 (``polynomials/newton_polynomial.py:10-11``, ``interpolation.py:15``,
 ``transformations/utils.py:10,18``) and the operator builders of ``LagrangeToNewton`` /
 ``NewtonToLagrange`` (``transformations/lagrange.py:23``, ``transformations/newton.py:32``).
-``uninstall()`` restores the originals.
+The callers either side of the path follow from the same rebinding: Lagrange arithmetic
+(``polynomials/lagrange_polynomial.py:29-187``) only composes the patched transformation and
+evaluation; the regression matrix (``extras/regression/ordinary_regression.py:8``) and
+``NewtonPolynomial.diff`` (``polynomials/newton_polynomial.py:12``) bind their kernels by name
+and are rebound here; ``MultiIndexSet.is_complete`` (``core/multi_index.py:20,128``) gets the
+linear-time completeness check.  ``uninstall()`` restores the originals.
 """
 import importlib
 
 from . import api
-from .polynomials import DDSOperator, NodeEvalOperator
+from .polynomials import DDSOperator, NodeEvalOperator, is_lexicographically_complete
 
 _saved = []
 
@@ -25,7 +30,9 @@ def install():
     mods = {n: importlib.import_module(n) for n in (
         "minterpy.utils", "minterpy.dds", "minterpy.interpolation",
         "minterpy.polynomials.newton_polynomial", "minterpy.transformations.utils",
-        "minterpy.transformations.lagrange", "minterpy.transformations.newton")}
+        "minterpy.transformations.lagrange", "minterpy.transformations.newton",
+        "minterpy.polynomials.utils", "minterpy.core.multi_index", "minterpy.core.utils",
+        "minterpy.extras.regression.ordinary_regression")}
     _set(mods["minterpy.utils"], "eval_newton_polynomials", api.eval_newton_polynomials)
     _set(mods["minterpy.utils"], "eval_newton_monomials", api.eval_newton_monomials)
     _set(mods["minterpy.polynomials.newton_polynomial"], "eval_newton_polynomials",
@@ -35,6 +42,14 @@ def install():
         _set(mods[name], "dds", api.dds)
     _set(mods["minterpy.transformations.utils"], "eval_newton_monomials",
          api.eval_newton_monomials)
+
+    reg = mods["minterpy.extras.regression.ordinary_regression"]
+    _set(reg, "eval_newton_polynomials", api.eval_newton_polynomials)
+    _set(reg, "eval_newton_monomials", api.eval_newton_monomials)
+    _set(mods["minterpy.polynomials.utils"], "deriv_newt_eval", api.deriv_newt_eval)
+    _set(mods["minterpy.polynomials.newton_polynomial"], "deriv_newt_eval", api.deriv_newt_eval)
+    for name in ("minterpy.core.utils", "minterpy.core.multi_index"):
+        _set(mods[name], "is_lexicographically_complete", is_lexicographically_complete)
 
     def l2n_operator(transformation):
         grid = transformation.grid

@@ -110,6 +110,33 @@ class Plan:
             _lib.check(rc)
         return out
 
+    def eval_deriv(self, xx, coeffs, orders):
+        """Partial derivative of the given orders (m ints): xx (P, m), coeffs (N, k) -> (P, k).
+        The device work is ``mpx_eval_deriv``; NumPy inputs are staged through torch."""
+        import torch
+        dev = torch.device("cuda", self.device)
+        as_numpy = not (_is_torch(xx) or _is_torch(coeffs))
+        orders = np.ascontiguousarray(orders, dtype=np.int32).reshape(-1)
+        if orders.shape[0] != self.m:
+            raise ValueError(f"{self.m} derivative orders expected, {orders.shape[0]} given")
+        x = torch.as_tensor(np.ascontiguousarray(xx) if not _is_torch(xx) else xx,
+                            dtype=torch.float64, device=dev)
+        c = torch.as_tensor(np.ascontiguousarray(coeffs) if not _is_torch(coeffs) else coeffs,
+                            dtype=torch.float64, device=dev)
+        if x.stride(-1) != 1:
+            x = x.contiguous()
+        if c.stride(-1) != 1:
+            c = c.contiguous()
+        P, k = x.shape[0], c.shape[1]
+        out = torch.empty((P, k), dtype=torch.float64, device=dev)
+        if P:
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            rc = _lib.lib().mpx_eval_deriv(self._h, x.data_ptr(), P, x.stride(0), c.data_ptr(), k,
+                                           c.stride(0), orders.ctypes.data, out.data_ptr(),
+                                           out.stride(0), stream)
+            _lib.check(rc)
+        return out.cpu().numpy() if as_numpy else out
+
     def monomials(self, xx, triangular=False):
         """(P, N) Newton monomial matrix."""
         import torch

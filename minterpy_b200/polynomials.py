@@ -1,7 +1,7 @@
 """Light host-side stand-ins for the reference's data model, for use where minterpy itself
-is not installed.  They only carry arrays -- index sets and generating points are produced
-by the reference (``MultiIndexSet.from_degree`` / ``Grid``) and handed over as arrays -- and
-route the hot path through the CUDA library:
+is not installed.  Index sets and generating points either come from the reference as arrays
+or from ``generators.py`` (``MultiIndexSet.from_degree``, ``Grid(mi)``: bit-identical to the
+reference's); the hot path runs in the CUDA library:
 
 * ``NewtonPolynomial.__call__``   ~ ``core/ABC/multivariate_polynomial_abstract.py:94-119``
   -> ``polynomials/newton_polynomial.py:30-54``
@@ -9,21 +9,48 @@ route the hot path through the CUDA library:
   ``transformations/newton.py:27-32``, ``core/ABC/transformation_abstract.py:84-180``
 * ``Interpolator`` / ``interpolate`` ~ ``interpolation.py:27-181``
 """
+import ctypes
+
 import numpy as np
 
-from . import api
+from . import api, generators
+from ._lib import check, lib
 from .plan import _is_torch, get_plan
 
 
+def is_lexicographically_complete(exponents):
+    """``core/utils.py:234-262`` for a sorted exponent matrix, through ``mpx_index_is_complete``
+    (host code of the library; one merge per dimension instead of the O(N^2 m) search)."""
+    e = np.ascontiguousarray(exponents, dtype=np.int64)
+    if e.ndim != 2:
+        raise ValueError("exponents must be a 2-D array (N x m)")
+    flag = ctypes.c_int(0)
+    check(lib().mpx_index_is_complete(e.ctypes.data, e.shape[0], e.shape[1], ctypes.byref(flag)))
+    return bool(flag.value)
+
+
 class MultiIndexSet:
-    """Holds a lexicographically sorted exponent matrix (N x m, int64)."""
+    """Holds a lexicographically sorted exponent matrix (N x m, int64)
+    (``core/multi_index.py``; only what the hot path reads)."""
 
     def __init__(self, exponents, lp_degree=None):
         exponents = np.asarray(exponents)
         if exponents.ndim != 2:
             raise ValueError("exponents must be a 2-D array (N x m)")
         self.exponents = np.ascontiguousarray(exponents, dtype=np.int64)
-        self.lp_degree = lp_degree
+        self.lp_degree = generators.verify_lp_degree(lp_degree)
+        self._poly_degree = None
+        self._is_complete = None
+
+    @classmethod
+    def from_degree(cls, spatial_dimension, poly_degree, lp_degree=None):
+        """``core/multi_index.py:70-77``."""
+        if type(poly_degree) is not int:
+            raise TypeError("only integer polynomial degrees are supported.")
+        if type(spatial_dimension) is not int:
+            raise TypeError("spatial dimension must be given as integer.")
+        lp = generators.verify_lp_degree(lp_degree)
+        return cls(generators.get_exponent_matrix(spatial_dimension, poly_degree, lp), lp_degree=lp)
 
     def __len__(self):
         return self.exponents.shape[0]
@@ -32,12 +59,34 @@ class MultiIndexSet:
     def spatial_dimension(self):
         return self.exponents.shape[1]
 
+    @property
+    def poly_degree(self):
+        if self._poly_degree is None:
+            self._poly_degree = generators.poly_degree_of(self.exponents, self.lp_degree)
+        return self._poly_degree
+
+    @property
+    def is_complete(self):
+        if self._is_complete is None:
+            self._is_complete = is_lexicographically_complete(self.exponents)
+        return self._is_complete
+
 
 class Grid:
-    """Index set + generating points; unisolvent nodes as in ``core/grid.py:19-24``."""
+    """Index set + generating points; unisolvent nodes as in ``core/grid.py:19-24``.  Without
+    generating points the Leja-ordered Chebyshev points of the set's polynomial degree are
+    used, as in ``core/grid.py:66-95``."""
 
-    def __init__(self, multi_index, generating_points):
+    def __init__(self, multi_index, generating_points=None, generating_values=None):
+        if not isinstance(multi_index, MultiIndexSet):
+            raise TypeError(f"the indices must be given as {MultiIndexSet} class instance")
         self.multi_index = multi_index
+        if generating_points is None:
+            if generating_values is None:
+                generating_values = generators.leja_ordered_chebyshev(multi_index.poly_degree)
+            generating_points = generators.generating_points_from_values(
+                multi_index.spatial_dimension, generating_values)
+        self.generating_values = generating_values
         gp = np.ascontiguousarray(generating_points, dtype=np.float64)
         if gp.ndim != 2 or gp.shape[1] != multi_index.spatial_dimension:
             raise ValueError("generating_points must be (n+1) x m")
@@ -79,8 +128,7 @@ class _Polynomial:
     def __init__(self, multi_index, coeffs, grid=None, generating_points=None):
         self.multi_index = multi_index
         if grid is None:
-            if generating_points is None:
-                raise ValueError("either grid or generating_points is required")
+            # no grid: the default one of the index set (Leja-ordered Chebyshev points)
             grid = Grid(multi_index, generating_points)
         self.grid = grid
         if coeffs is not None and coeffs.shape[0] != len(multi_index):
@@ -102,10 +150,79 @@ class NewtonPolynomial(_Polynomial):
         return api.eval_newton_polynomials(x, self.coeffs, self.multi_index.exponents,
                                            self.grid.generating_points, verify_input=api.DEBUG)
 
+    def diff(self, order):
+        """``polynomials/newton_polynomial.py:68-86``: the derivative's values on the
+        unisolvent nodes (its Lagrange coefficients), then divided differences.  Both steps
+        run on the device; torch coefficients stay there."""
+        order = np.asarray(order).reshape(-1)
+        if order.shape[0] != self.spatial_dimension:
+            raise ValueError(f"inconsistent number of elements in 'order': "
+                             f"{order.shape[0]} given, {self.spatial_dimension} expected")
+        nodes = self.grid.unisolvent_nodes
+        if _is_torch(self.coeffs):
+            import torch
+            nodes = torch.as_tensor(nodes, device=self.coeffs.device)
+        lag = api.deriv_newt_eval(nodes, self.coeffs, self.multi_index.exponents,
+                                  self.grid.generating_points, order)
+        newt = api.dds(lag, self.grid.tree)
+        if self.coeffs.ndim == 1:
+            newt = newt.reshape(-1)
+        return NewtonPolynomial(self.multi_index, newt, grid=self.grid)
+
+    def partial_diff(self, dim, order=1):
+        """``polynomials/newton_polynomial.py:55-66``."""
+        if not 0 <= dim < self.spatial_dimension:
+            raise ValueError(f"dimension {dim} is out of range for a {self.spatial_dimension}-"
+                             f"dimensional polynomial")
+        orders = np.zeros(self.spatial_dimension, dtype=np.int64)
+        orders[dim] = order
+        return self.diff(orders)
+
 
 class LagrangePolynomial(_Polynomial):
     """Coefficients are the values on the unisolvent nodes (no direct evaluation, as in the
-    reference: ``polynomials/lagrange_polynomial.py``)."""
+    reference: ``polynomials/lagrange_polynomial.py``).
+
+    ``+``, ``-`` and ``*`` follow ``polynomials/lagrange_polynomial.py:29-187``: both operands
+    go to the Newton basis (dds kernel), a result index set and its default grid are generated
+    (sum/difference: the larger degree and lp-degree; product: the SUM of the degrees and of the
+    lp-degrees, as the reference does), both Newton polynomials are evaluated on the result's
+    unisolvent nodes (evaluation kernel) and the values are combined there.  With torch
+    coefficients nothing but the node coordinates crosses the host-device boundary."""
+
+    def _combine(self, other, what):
+        if not isinstance(other, LagrangePolynomial):
+            return NotImplemented
+        if other.spatial_dimension != self.spatial_dimension:
+            raise NotImplementedError("operands of different spatial dimension are not supported")
+        newt_a = LagrangeToNewton(self)()
+        newt_b = LagrangeToNewton(other)()
+        mi_a, mi_b = self.multi_index, other.multi_index
+        if what == "mul":
+            degree = int(mi_a.poly_degree + mi_b.poly_degree)
+            lp = mi_a.lp_degree + mi_b.lp_degree
+        else:
+            degree = int(max(mi_a.poly_degree, mi_b.poly_degree))
+            lp = max(mi_a.lp_degree, mi_b.lp_degree)
+        res_mi = MultiIndexSet.from_degree(self.spatial_dimension, degree, lp)
+        res_grid = Grid(res_mi)
+        nodes = res_grid.unisolvent_nodes
+        if _is_torch(self.coeffs) or _is_torch(other.coeffs):
+            import torch
+            ref = self.coeffs if _is_torch(self.coeffs) else other.coeffs
+            nodes = torch.as_tensor(nodes, device=ref.device)
+        va, vb = newt_a(nodes), newt_b(nodes)
+        res = va + vb if what == "add" else va - vb if what == "sub" else va * vb
+        return LagrangePolynomial(res_mi, res, grid=res_grid)
+
+    def __add__(self, other):
+        return self._combine(other, "add")
+
+    def __sub__(self, other):
+        return self._combine(other, "sub")
+
+    def __mul__(self, other):
+        return self._combine(other, "mul")
 
 
 class _Transformation:
@@ -221,6 +338,13 @@ class Interpolator:
         return NewtonPolynomial(self.multi_index, coeffs, grid=self.grid)
 
 
-def interpolate(fct, grid):
-    """``interpolation.py:161-181``; the grid (index set + generating points) is given."""
-    return Interpolator(grid)(fct)
+def interpolate(fct, spatial_dimension, poly_degree=None, lp_degree=None):
+    """``interpolation.py:161-181``: ``interpolate(fct, spatial_dimension, poly_degree,
+    lp_degree)`` builds the index set and its default grid; ``interpolate(fct, grid)`` takes a
+    ready grid (arrays that came from the reference).  Returns the Newton interpolant."""
+    if isinstance(spatial_dimension, Grid):
+        return Interpolator(spatial_dimension)(fct)
+    if poly_degree is None:
+        raise TypeError("interpolate(fct, spatial_dimension, poly_degree[, lp_degree])")
+    mi = MultiIndexSet.from_degree(spatial_dimension, poly_degree, lp_degree)
+    return Interpolator(Grid(mi))(fct)

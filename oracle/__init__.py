@@ -45,6 +45,9 @@ def _load():
         lib.orc_dds.restype = ctypes.c_int
         lib.orc_dds.argtypes = [_dp, _i64, ctypes.c_int, _ip, ctypes.c_int, _dp, _i64]
         lib.orc_num_threads.restype = ctypes.c_int
+        lib.orc_deriv_newt_eval.restype = ctypes.c_int
+        lib.orc_deriv_newt_eval.argtypes = [_dp, _i64, _dp, ctypes.c_int, _ip, _i64,
+                                            ctypes.c_int, _dp, _i64, _ip, _dp]
         _lib = lib
     return _lib
 
@@ -104,6 +107,23 @@ def dds(fct_values, exponents, generating_points):
                          gp.shape[0])
     _check(rc, "dds")
     return v
+
+
+def deriv_newt_eval(xx, coefficients, exponents, generating_points, derivative_order_along):
+    """(P, k) values of the partial derivative -- ``minterpy/polynomials/utils.py:8-112``
+    (the reference returns (P,) for its single coefficient vector)."""
+    e = np.ascontiguousarray(exponents, dtype=np.int64)
+    gp = _f64(generating_points)
+    N, m = e.shape
+    xx = _f64(xx).reshape(-1, m)
+    c = _f64(coefficients).reshape(N, -1)
+    orders = np.ascontiguousarray(derivative_order_along, dtype=np.int64).reshape(m)
+    out = np.empty((xx.shape[0], c.shape[1]))
+    rc = _load().orc_deriv_newt_eval(_ptr(xx, _dp), xx.shape[0], _ptr(c, _dp), c.shape[1],
+                                     _ptr(e, _ip), N, m, _ptr(gp, _dp), gp.shape[0],
+                                     _ptr(orders, _ip), _ptr(out, _dp))
+    _check(rc, "deriv_newt_eval")
+    return out
 
 
 def num_threads():

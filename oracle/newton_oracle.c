@@ -9,7 +9,8 @@
  * outputs of the unmodified reference (imported from /root/reference/src by
  * tests/golden/make_golden.py, which is committed together with the vectors it wrote to
  * tests/golden/).  eval: <= 1e-13 * max|ref| (the reference ends in a BLAS product whose
- * summation order is unspecified); monomials and dds: bit-exact.
+ * summation order is unspecified), derivative evaluation likewise; monomials and dds:
+ * bit-exact.
  *
  * Each function cites the reference code it restates (paths relative to /root/reference).
  * Arithmetic is plain IEEE double; build with -ffp-contract=off so gcc cannot fuse a*b+c
@@ -164,6 +165,97 @@ int orc_eval_newton_polynomials(const double *xx, int64_t P, const double *coeff
 }
 
 /* lexicographic compare, last column most significant: core/utils.py:44-92 (np.lexsort) */
+/*
+ * deriv_newt_eval(x, coefficients, exponents, generating_points, derivative_order_along)
+ *   src/minterpy/polynomials/utils.py:8-112
+ * Per point and dimension i with order o = orders[i] > 0 the table entry q becomes
+ *   o! * sum over all (q-o)-element subsets S of {0..q-1}, in itertools.combinations order,
+ *        of prod_{t in S} (x_i - gp[t, i])                       (:84-93)
+ * with entries below o equal to 0 and entry o equal to o! (:73-82; when o is not smaller
+ * than the table height nothing else is written, :76-77); dimensions with o == 0 keep the
+ * chained products (:61-68).  A monomial whose exponent is 0 in a differentiated dimension
+ * is 0 (:104-108).  The result is the dot product with the coefficients (:110; BLAS order is
+ * unspecified, summed here j = 0..N-1).  coeffs (N x k) -- the reference takes k = 1 only.
+ * The subset sum costs C(q, o) products: keep q and o small in tests.
+ */
+static double factorial_as_double(int64_t o)
+{
+    double f = 1.0;                       /* exact up to 22!, beyond that rounded like float(int) */
+    for (int64_t t = 2; t <= o; ++t) f *= (double)t;
+    return f;
+}
+
+/* sum over r-subsets of the first q factors, subsets in lexicographic order */
+static double subset_product_sum(const double *factors, int64_t q, int64_t r)
+{
+    int64_t idx[256];
+    double res = 0.0;
+    for (int64_t t = 0; t < r; ++t) idx[t] = t;
+    for (;;) {
+        double prod = 1.0;                /* np.prod of the chosen factors, left to right */
+        for (int64_t t = 0; t < r; ++t) prod *= factors[idx[t]];
+        res += prod;
+        int64_t t = r - 1;
+        while (t >= 0 && idx[t] == q - r + t) --t;
+        if (t < 0) break;
+        ++idx[t];
+        for (int64_t u = t + 1; u < r; ++u) idx[u] = idx[u - 1] + 1;
+    }
+    return res;
+}
+
+int orc_deriv_newt_eval(const double *xx, int64_t P, const double *coeffs, int k,
+                        const int64_t *e, int64_t N, int m, const double *gp, int64_t gp_rows,
+                        const int64_t *orders, double *out)
+{
+    int64_t mx[64];
+    if (m < 1 || m > 64 || N < 1 || k < 1) return 1;
+    max_exponents(e, N, m, mx);
+    for (int i = 0; i < m; ++i) if (mx[i] > gp_rows || mx[i] > 255 || orders[i] < 0) return 2;
+    const int64_t rows = maxmax(mx, m) + 1;            /* num_prods */
+    double *products = calloc((size_t)rows * m, sizeof(double));
+    double *factors = malloc(sizeof(double) * 256);
+    if (!products || !factors) { free(products); free(factors); return 3; }
+    for (int64_t p = 0; p < P; ++p) {
+        const double *x = xx + p * m;
+        for (int i = 0; i < m; ++i) {
+            const int64_t o = orders[i];
+            if (o == 0) {
+                double prod = 1.0;
+                for (int64_t j = 0; j < mx[i]; ++j) {
+                    prod *= x[i] - gp[j * m + i];
+                    products[(j + 1) * m + i] = prod;
+                }
+                continue;
+            }
+            for (int64_t j = 0; j < o && j < rows; ++j) products[j * m + i] = 0.0;
+            if (o >= rows) continue;
+            const double fact = factorial_as_double(o);
+            products[o * m + i] = fact;
+            for (int64_t q = o + 1; q <= mx[i]; ++q) {
+                for (int64_t t = 0; t < q; ++t) factors[t] = x[i] - gp[t * m + i];
+                double res = subset_product_sum(factors, q, q - o);
+                res *= fact;
+                products[q * m + i] = res;
+            }
+        }
+        double *o_row = out + p * k;
+        for (int q = 0; q < k; ++q) o_row[q] = 0.0;
+        for (int64_t j = 0; j < N; ++j) {
+            double v = 1.0;
+            for (int i = 0; i < m; ++i) {
+                const int64_t ex = e[j * m + i];
+                if (ex > 0) v *= products[ex * m + i];
+                else if (orders[i] > 0) v = 0.0;
+            }
+            for (int q = 0; q < k; ++q) o_row[q] += coeffs[j * k + q] * v;
+        }
+    }
+    free(products);
+    free(factors);
+    return 0;
+}
+
 static int lex_cmp(const int64_t *a, const int64_t *b, int m)
 {
     for (int i = m - 1; i >= 0; --i) {

@@ -93,3 +93,24 @@ def test_incomplete_set_rejected():
     gp = np.zeros((3, 2)); gp[:, 0] = [0.0, 1.0, -1.0]; gp[:, 1] = [0.0, -1.0, 1.0]
     with pytest.raises(ValueError):
         oracle.dds(np.ones(2), e, gp)
+
+
+def test_derivative_evaluation_against_reference():
+    """orc_deriv_newt_eval against deriv_newt_eval of the reference
+    (src/minterpy/polynomials/utils.py:8-112); the final dot product is BLAS in the reference,
+    so parity is <= 1e-13 * max|ref| per derivative (exact zeros must be exact zeros)."""
+    d = golden_io.load("next_rows")
+    assert len(d["der/tags"]) >= 6
+    for tag in d["der/tags"]:
+        e, gp = d[f"der/{tag}/exponents"], d[f"der/{tag}/generating_points"]
+        x, c = d[f"der/{tag}/x"], d[f"der/{tag}/coeffs"]
+        for o, want in zip(d[f"der/{tag}/orders"], d[f"der/{tag}/values_ref"]):
+            got = oracle.deriv_newt_eval(x, c, e, gp, o)[:, 0]
+            scale = np.abs(want).max()
+            if scale == 0.0:
+                assert not got.any()
+            else:
+                assert np.abs(got - want).max() <= 1e-13 * scale, (tag, o)
+        # order zero is the polynomial itself
+        plain = oracle.eval_newton_polynomials(x, c, e, gp)[:, 0]
+        assert np.array_equal(oracle.deriv_newt_eval(x, c, e, gp, np.zeros(e.shape[1]))[:, 0], plain)

@@ -9,39 +9,19 @@ own call stack (`NewtonPolynomial.__call__`, `interpolate`, `LagrangeToNewton`,
 import numpy as np
 import pytest
 
-import oracle
+from oracle_plan import fake_get_plan
 from ref_shim import load_reference
 
 mp = load_reference()
 pytestmark = pytest.mark.skipif(mp is None, reason="reference not available")
 
 
-class OraclePlan:
-    """Same interface as minterpy_b200.plan.Plan, computed by the CPU oracle."""
-
-    def __init__(self, exponents, generating_points):
-        self.e = np.ascontiguousarray(exponents, dtype=np.int64)
-        self.gp = np.ascontiguousarray(generating_points, dtype=np.float64)
-
-    is_complete = True
-
-    def eval(self, xx, coeffs):
-        return oracle.eval_newton_polynomials(xx, coeffs, self.e, self.gp)
-
-    def monomials(self, xx, triangular=False):
-        return oracle.eval_newton_monomials(xx, self.e, self.gp, triangular)
-
-    def dds(self, values):
-        return oracle.dds(values, self.e, self.gp)
-
-
 @pytest.fixture()
 def patched(monkeypatch):
     import minterpy_b200
     from minterpy_b200 import api, polynomials
-    fake = lambda e, gp, device=None: OraclePlan(e, gp)          # noqa: E731
-    monkeypatch.setattr(api, "get_plan", fake)
-    monkeypatch.setattr(polynomials, "get_plan", fake)
+    monkeypatch.setattr(api, "get_plan", fake_get_plan)
+    monkeypatch.setattr(polynomials, "get_plan", fake_get_plan)
     minterpy_b200.install()
     yield minterpy_b200
     minterpy_b200.uninstall()
@@ -109,3 +89,58 @@ def test_errors_through_reference_stack(patched):
         poly(pts[:, :2])
     with pytest.raises(TypeError):
         poly(pts.astype(np.float32))
+
+
+def test_lagrange_arithmetic_through_reference_stack(patched):
+    """polynomials/lagrange_polynomial.py:29-187 composes L2N + evaluation: with the path
+    rebound the reference's own `+ - *` give the unpatched results."""
+    rng = np.random.default_rng(3)
+    mi_a = mp.MultiIndexSet.from_degree(2, 3, 1.0)
+    mi_b = mp.MultiIndexSet.from_degree(2, 2, 2.0)
+    a = mp.LagrangePolynomial(mi_a, rng.uniform(-1, 1, len(mi_a)))
+    b = mp.LagrangePolynomial(mi_b, rng.uniform(-1, 1, len(mi_b)))
+    got = [(a + b).coeffs, (a - b).coeffs, (a * b).coeffs]
+    patched.uninstall()
+    want = [(a + b).coeffs, (a - b).coeffs, (a * b).coeffs]
+    for g, w in zip(got, want):
+        assert g.shape == w.shape
+        np.testing.assert_allclose(g, w, rtol=0, atol=1e-12 * max(1.0, np.max(np.abs(w))))
+
+
+def test_diff_and_regression_through_reference_stack(patched):
+    from minterpy.extras.regression import OrdinaryRegression
+    rng = np.random.default_rng(4)
+    mi = mp.MultiIndexSet.from_degree(3, 3, 2.0)
+    poly = mp.NewtonPolynomial(mi, rng.uniform(-1, 1, len(mi)))
+    xx = rng.uniform(-1, 1, (80, 3))
+    yy = np.cos(xx @ np.array([1.0, 2.0, 0.5]))
+    got_d = poly.diff(np.array([1, 0, 2])).coeffs
+    got_p = poly.partial_diff(1).coeffs
+    reg = OrdinaryRegression(mi)
+    reg.fit(xx, yy)
+    got_r, got_c = reg._regression_matrix, reg._coeffs
+    regn = OrdinaryRegression(mi, origin_poly=mp.NewtonPolynomial)
+    regn.fit(xx, yy)
+    got_rn = regn._regression_matrix
+    patched.uninstall()
+    np.testing.assert_allclose(got_d, poly.diff(np.array([1, 0, 2])).coeffs, rtol=0, atol=1e-11)
+    np.testing.assert_allclose(got_p, poly.partial_diff(1).coeffs, rtol=0, atol=1e-11)
+    ref = OrdinaryRegression(mi)
+    ref.fit(xx, yy)
+    np.testing.assert_allclose(got_r, ref._regression_matrix, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(got_c, ref._coeffs, rtol=0, atol=1e-9)
+    refn = OrdinaryRegression(mi, origin_poly=mp.NewtonPolynomial)
+    refn.fit(xx, yy)
+    assert np.array_equal(got_rn, refn._regression_matrix)
+
+
+def test_completeness_check_is_rebound(patched):
+    import minterpy.core.multi_index as mim
+    from minterpy_b200.polynomials import is_lexicographically_complete
+    assert mim.is_lexicographically_complete is is_lexicographically_complete
+    e = mp.MultiIndexSet.from_degree(3, 3, 2.0).exponents
+    holed = mp.MultiIndexSet(np.delete(e, 4, axis=0), lp_degree=2.0)
+    assert mp.MultiIndexSet(e, lp_degree=2.0).is_complete and not holed.is_complete
+    patched.uninstall()
+    assert mim.is_lexicographically_complete is not is_lexicographically_complete
+    assert not mp.MultiIndexSet(np.delete(e, 4, axis=0), lp_degree=2.0).is_complete
