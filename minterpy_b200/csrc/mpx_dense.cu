@@ -3,69 +3,128 @@
 // T is (rows x cols); for the transformations of this path it is N x N, read once from HBM
 // (8 N^2 bytes) and that read bounds the kernel for every k the library meets.  A CTA owns
 // 32 rows; a warp owns 4 of them and sweeps the columns, each lane keeping KT partial sums per
-// row, reduced by shuffles at the end.
+// row, reduced by shuffles at the end.  The coefficient rows a span of columns needs are staged
+// transposed in shared memory by the whole CTA (one barrier per 64 KB of matrix), so the inner
+// loop reads them with conflict-free 16-byte loads whatever k and ld_c are.
 #include "mpx_common.h"
 
 namespace {
 
 constexpr int ROWS_PER_WARP = 4;
 constexpr int WARPS = 8;
-constexpr int KT = 4;     // columns of c per pass
-constexpr int UNR = 4;    // column strips of 64 in flight per row (double2 loads)
+constexpr int NTHREADS = WARPS * 32;
+constexpr int UNR = 4;            // column strips of 64 in flight per row (double2 loads)
+constexpr int SPAN = 64 * UNR;    // columns per staged span
+constexpr int CS = SPAN + 4;      // pitch of a staged coefficient row (two columns of overlap)
 
 // lanes sweep the columns two at a time (16-byte loads), UNR strips per row are issued before
-// any of them is used: 4 rows x 4 strips x 16 B = 256 B in flight per lane
-__global__ void __launch_bounds__(WARPS * 32)
+// any of them is used: 4 rows x 4 strips x 16 B = 256 B in flight per lane.
+// ODD: the leading dimension is odd (the usual case, N x N with N odd), so rows start
+// alternately 0 and 8 bytes past a 16-byte boundary.  A warp's first row is a multiple of 4,
+// hence its rows 0 and 2 are aligned and rows 1 and 3 are not: those load their pairs one
+// column further right (columns j+1, j+2 instead of j, j+1), their column 0 is added by lane 0.
+// KT = coefficient columns per pass (grid.y covers k in steps of KT).
+template <bool ODD, int KT>
+__global__ void __launch_bounds__(NTHREADS)
 dense_apply_kernel(const double *__restrict__ T, int64_t rows, int64_t cols, int64_t ld_t,
                    const double *__restrict__ c, int k, int64_t ld_c, double *__restrict__ out,
                    int64_t ld_out)
 {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ __align__(16) double cs[2][KT][CS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t r0 = ((int64_t)blockIdx.x * WARPS + warp) * ROWS_PER_WARP;
     const int q0 = blockIdx.y * KT;
-    if (r0 >= rows) return;
+    const bool active = r0 < rows;
+    // the last warp may own fewer than 4 real rows; its stand-in rows do not follow the
+    // alignment pattern, so it takes the plain loop at the bottom for all columns
+    const bool full = r0 + ROWS_PER_WARP <= rows;
     double acc[ROWS_PER_WARP][KT];
 #pragma unroll
     for (int i = 0; i < ROWS_PER_WARP; ++i)
 #pragma unroll
         for (int q = 0; q < KT; ++q) acc[i][q] = 0.0;
-    const bool vec_ok = ((ld_t & 1) == 0) && ((reinterpret_cast<uintptr_t>(T) & 15) == 0);
-    int64_t j0 = 0;
-    if (vec_ok) {
-        const int64_t span = 64 * UNR;
-        for (; j0 + span <= cols; j0 += span) {
+    const double *row[ROWS_PER_WARP];
+#pragma unroll
+    for (int i = 0; i < ROWS_PER_WARP; ++i) row[i] = T + ((r0 + i < rows) ? r0 + i : rows - 1) * ld_t;
+
+    constexpr int STAGE = (SPAN + 2) * KT;                    // staged doubles per span
+    constexpr int NS = (STAGE + NTHREADS - 1) / NTHREADS;     // of them per thread
+    const int64_t n_spans = (cols - (ODD ? 1 : 0)) / SPAN;    // spans with SPAN (+1) columns left
+    double creg[NS];
+    auto stage_load = [&](int64_t sp) {
+#pragma unroll
+        for (int n = 0; n < NS; ++n) {
+            const int idx = tid + n * NTHREADS;
+            const int jj = idx / KT, q = idx % KT;
+            const int64_t col = sp * SPAN + jj;
+            creg[n] = (idx < STAGE && col < cols && q0 + q < k) ? c[col * ld_c + q0 + q] : 0.0;
+        }
+    };
+    auto stage_store = [&](int buf) {
+#pragma unroll
+        for (int n = 0; n < NS; ++n) {
+            const int idx = tid + n * NTHREADS;
+            if (idx < STAGE) cs[buf][idx % KT][idx / KT] = creg[n];
+        }
+    };
+    if (n_spans > 0) {
+        stage_load(0);
+        stage_store(0);
+    }
+    __syncthreads();
+    for (int64_t sp = 0; sp < n_spans; ++sp) {
+        const int buf = (int)(sp & 1);
+        const int64_t j0 = sp * SPAN;
+        if (sp + 1 < n_spans) stage_load(sp + 1);
+        if (full) {
             double2 t[ROWS_PER_WARP][UNR];
 #pragma unroll
-            for (int i = 0; i < ROWS_PER_WARP; ++i) {
-                const int64_t r = (r0 + i < rows) ? r0 + i : rows - 1;
+            for (int i = 0; i < ROWS_PER_WARP; ++i)
 #pragma unroll
                 for (int u = 0; u < UNR; ++u)
-                    t[i][u] = __ldcs(reinterpret_cast<const double2 *>(T + r * ld_t + j0 + 64 * u + 2 * lane));
-            }
+                    t[i][u] = __ldcs(reinterpret_cast<const double2 *>(
+                        row[i] + j0 + 64 * u + 2 * lane + ((ODD && (i & 1)) ? 1 : 0)));
 #pragma unroll
             for (int u = 0; u < UNR; ++u) {
-                const int64_t j = j0 + 64 * u + 2 * lane;
-                double cx[KT], cy[KT];
+                const int jj = 64 * u + 2 * lane;
 #pragma unroll
                 for (int q = 0; q < KT; ++q) {
-                    cx[q] = (q0 + q < k) ? c[j * ld_c + q0 + q] : 0.0;
-                    cy[q] = (q0 + q < k) ? c[(j + 1) * ld_c + q0 + q] : 0.0;
+                    const double2 c01 = *reinterpret_cast<const double2 *>(&cs[buf][q][jj]);
+                    const double c2 = ODD ? cs[buf][q][jj + 2] : 0.0;
+#pragma unroll
+                    for (int i = 0; i < ROWS_PER_WARP; ++i) {
+                        const bool shifted = ODD && (i & 1);
+                        acc[i][q] = fma(t[i][u].y, shifted ? c2 : c01.y,
+                                        fma(t[i][u].x, shifted ? c01.y : c01.x, acc[i][q]));
+                    }
                 }
+            }
+        }
+        if (sp + 1 < n_spans) stage_store(buf ^ 1);
+        __syncthreads();
+    }
+    if (!active) return;
+    int64_t j0 = 0;
+    if (full) {
+        j0 = n_spans * SPAN;
+        if (ODD && lane == 0) {                  // column 0 of the shifted rows
 #pragma unroll
-                for (int i = 0; i < ROWS_PER_WARP; ++i)
-#pragma unroll
-                    for (int q = 0; q < KT; ++q)
-                        acc[i][q] = fma(t[i][u].y, cy[q], fma(t[i][u].x, cx[q], acc[i][q]));
+            for (int q = 0; q < KT; ++q) {
+                const double cv = (q0 + q < k) ? c[q0 + q] : 0.0;
+                acc[1][q] = fma(row[1][0], cv, acc[1][q]);
+                acc[3][q] = fma(row[3][0], cv, acc[3][q]);
             }
         }
     }
-    for (int64_t j = j0 + lane; j < cols; j += 32) {          // remainder / unaligned matrices
+    // remaining columns: [j0, cols) for the unshifted rows, [j0 + 1, cols) for the shifted ones
+    for (int64_t j = j0 + lane; j < cols; j += 32) {
         double cv[KT];
 #pragma unroll
         for (int q = 0; q < KT; ++q) cv[q] = (q0 + q < k) ? c[j * ld_c + q0 + q] : 0.0;
 #pragma unroll
         for (int i = 0; i < ROWS_PER_WARP; ++i) {
-            const double t = (r0 + i < rows) ? T[(r0 + i) * ld_t + j] : 0.0;
+            if (ODD && full && (i & 1) && j == j0) continue;
+            const double t = row[i][j];
 #pragma unroll
             for (int q = 0; q < KT; ++q) acc[i][q] = fma(t, cv[q], acc[i][q]);
         }
@@ -81,6 +140,74 @@ dense_apply_kernel(const double *__restrict__ T, int64_t rows, int64_t cols, int
         }
 }
 
+// the matrix itself is not 16-byte aligned (a view that starts at an odd column): 8-byte
+// loads, 4 strips of 32 columns in flight per row, 4 coefficient columns per pass
+constexpr int KT_PLAIN = 4;
+__global__ void __launch_bounds__(NTHREADS)
+dense_apply_plain_kernel(const double *__restrict__ T, int64_t rows, int64_t cols, int64_t ld_t,
+                         const double *__restrict__ c, int k, int64_t ld_c,
+                         double *__restrict__ out, int64_t ld_out)
+{
+    constexpr int KT = KT_PLAIN;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t r0 = ((int64_t)blockIdx.x * WARPS + warp) * ROWS_PER_WARP;
+    const int q0 = blockIdx.y * KT;
+    if (r0 >= rows) return;
+    double acc[ROWS_PER_WARP][KT];
+#pragma unroll
+    for (int i = 0; i < ROWS_PER_WARP; ++i)
+#pragma unroll
+        for (int q = 0; q < KT; ++q) acc[i][q] = 0.0;
+    const double *row[ROWS_PER_WARP];
+#pragma unroll
+    for (int i = 0; i < ROWS_PER_WARP; ++i) row[i] = T + ((r0 + i < rows) ? r0 + i : rows - 1) * ld_t;
+    int64_t j0 = 0;
+    for (; j0 + 32 * UNR <= cols; j0 += 32 * UNR) {
+        double t[ROWS_PER_WARP][UNR];
+#pragma unroll
+        for (int i = 0; i < ROWS_PER_WARP; ++i)
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) t[i][u] = __ldcs(row[i] + j0 + 32 * u + lane);
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            const int64_t j = j0 + 32 * u + lane;
+#pragma unroll
+            for (int q = 0; q < KT; ++q) {
+                const double cv = (q0 + q < k) ? c[j * ld_c + q0 + q] : 0.0;
+#pragma unroll
+                for (int i = 0; i < ROWS_PER_WARP; ++i) acc[i][q] = fma(t[i][u], cv, acc[i][q]);
+            }
+        }
+    }
+    for (int64_t j = j0 + lane; j < cols; j += 32) {
+#pragma unroll
+        for (int q = 0; q < KT; ++q) {
+            const double cv = (q0 + q < k) ? c[j * ld_c + q0 + q] : 0.0;
+#pragma unroll
+            for (int i = 0; i < ROWS_PER_WARP; ++i) acc[i][q] = fma(row[i][j], cv, acc[i][q]);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < ROWS_PER_WARP; ++i)
+#pragma unroll
+        for (int q = 0; q < KT; ++q) {
+            double v = acc[i][q];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0 && r0 + i < rows && q0 + q < k) out[(r0 + i) * ld_out + q0 + q] = v;
+        }
+}
+
+template <int KT>
+void launch_vec(bool odd, dim3 grid, cudaStream_t st, const double *T, int64_t rows, int64_t cols,
+                int64_t ld_t, const double *c, int k, int64_t ld_c, double *out, int64_t ld_out)
+{
+    if (odd)
+        dense_apply_kernel<true, KT><<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out);
+    else
+        dense_apply_kernel<false, KT><<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out);
+}
+
 }  // namespace
 
 extern "C" int mpx_apply_dense(int device, const double *T, int64_t rows, int64_t cols,
@@ -94,9 +221,23 @@ extern "C" int mpx_apply_dense(int device, const double *T, int64_t rows, int64_
     DeviceGuard dg(device);
     if (!dg.ok) return mpx_fail(MPX_ERR_CUDA, "cannot select CUDA device");
     const int64_t rows_per_cta = (int64_t)WARPS * ROWS_PER_WARP;
-    dim3 grid((unsigned)((rows + rows_per_cta - 1) / rows_per_cta), (unsigned)((k + KT - 1) / KT), 1);
-    dense_apply_kernel<<<grid, WARPS * 32, 0, (cudaStream_t)stream>>>(T, rows, cols, ld_t, c, k, ld_c,
-                                                                    out, ld_out);
+    const unsigned gx = (unsigned)((rows + rows_per_cta - 1) / rows_per_cta);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool aligned = (reinterpret_cast<uintptr_t>(T) & 15) == 0;
+    if (!aligned) {
+        dim3 grid(gx, (unsigned)((k + KT_PLAIN - 1) / KT_PLAIN), 1);
+        dense_apply_plain_kernel<<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out);
+    } else {
+        const bool odd = (ld_t & 1) != 0;
+        const int kt = k >= 8 ? 8 : k >= 3 ? 4 : k;          // coefficient columns per pass
+        dim3 grid(gx, (unsigned)((k + kt - 1) / kt), 1);
+        switch (kt) {
+        case 1: launch_vec<1>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out); break;
+        case 2: launch_vec<2>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out); break;
+        case 4: launch_vec<4>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out); break;
+        default: launch_vec<8>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out); break;
+        }
+    }
     MPX_CUDA(cudaGetLastError());
     return MPX_OK;
 }

@@ -256,7 +256,8 @@ def test_dense_apply(mpb):
     import torch
     from minterpy_b200 import _lib
     rng = np.random.default_rng(2)
-    for rows, cols, k in ((1, 1, 1), (70, 70, 1), (130, 97, 5), (513, 513, 9)):
+    for rows, cols, k in ((1, 1, 1), (70, 70, 1), (130, 97, 5), (513, 513, 9), (3, 1025, 2),
+                          (515, 700, 3), (1027, 1301, 4), (258, 257, 1)):
         T = np.tril(rng.uniform(-1, 1, (rows, cols)))
         c = rng.uniform(-1, 1, (cols, k))
         Tt, ct = torch.from_numpy(T).cuda(), torch.from_numpy(c).cuda()
@@ -265,6 +266,19 @@ def test_dense_apply(mpb):
                                         out.data_ptr(), k, None)
         _lib.check(rc)
         assert rel_err(out.cpu().numpy(), T @ c) <= 1e-13
+    # a view into a wider matrix: leading dimension larger than the column count, and a base
+    # address that is only 8-byte aligned (first column dropped)
+    wide = rng.uniform(-1, 1, (301, 1200))
+    Wt = torch.from_numpy(wide).cuda()
+    for first, cols in ((0, 1199), (1, 1199), (1, 700), (2, 1001)):
+        c = rng.uniform(-1, 1, (cols, 3))
+        ct = torch.from_numpy(c).cuda()
+        out = torch.empty((301, 3), dtype=torch.float64, device="cuda")
+        view = Wt[:, first:first + cols]
+        rc = _lib.lib().mpx_apply_dense(0, view.data_ptr(), 301, cols, 1200, ct.data_ptr(), 3, 3,
+                                        out.data_ptr(), 3, None)
+        _lib.check(rc)
+        assert rel_err(out.cpu().numpy(), wide[:, first:first + cols] @ c) <= 1e-13
 
 
 @pytest.mark.parametrize("k", [8, 9, 16, 31, 64, 100])

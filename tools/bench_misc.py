@@ -31,6 +31,15 @@ def timed(fn, iters=10):
 
 
 def main():
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="", help="comma list of: fill, monomials, dense")
+    ap.add_argument("--iters", type=int, default=10)
+    args = ap.parse_args()
+    only = set(filter(None, args.only.split(",")))
+
+    def want(name):
+        return not only or name in only
     import torch
     import minterpy_b200 as mpb
     from minterpy_b200 import _lib
@@ -42,12 +51,13 @@ def main():
         hbm, src = 6650.0, "fallback"
     stream = torch.cuda.current_stream().cuda_stream
     # context: what a pure write stream reaches on this GPU (torch fill of 8 GB)
-    buf = torch.empty(1 << 30, dtype=torch.float64, device="cuda")
-    ms = timed(lambda: buf.fill_(1.0))
-    print(json.dumps({"bench": "write_only_fill", "bytes": 8 << 30, "ms": ms,
-                      "GBps": (8 << 30) / (ms * 1e-3) / 1e9, "hbm_copy_peak": hbm}))
-    del buf
-    for tag, P in (("cfg2", 40000), ("cfg3", 100000)):
+    if want("fill"):
+        buf = torch.empty(1 << 30, dtype=torch.float64, device="cuda")
+        ms = timed(lambda: buf.fill_(1.0))
+        print(json.dumps({"bench": "write_only_fill", "bytes": 8 << 30, "ms": ms,
+                          "GBps": (8 << 30) / (ms * 1e-3) / 1e9, "hbm_copy_peak": hbm}))
+        del buf
+    for tag, P in (("cfg2", 40000), ("cfg3", 100000)) if want("monomials") else ():
         g = golden_io.load(tag)
         e, gp = g["exponents"], g["generating_points"]
         N, m = e.shape
@@ -57,7 +67,7 @@ def main():
 
         def run():
             _lib.check(lib.mpx_monomials(plan._h, xx.data_ptr(), P, m, out.data_ptr(), N, 0, stream))
-        ms = timed(run)
+        ms = timed(run, args.iters)
         gbs = P * N * 8 / (ms * 1e-3) / 1e9
         print(json.dumps({"bench": "monomials", "workload": tag, "P": P, "N": int(N), "ms": ms,
                           "pm_per_s": P * N / (ms * 1e-3),
@@ -65,7 +75,7 @@ def main():
                                        "frac": gbs / hbm, "peak_source": src},
                           "l2": "output (8 B x P x N) larger than L2"}))
         del out
-    for rows, k in ((24809, 1), (24809, 8)):
+    for rows, k in ((24809, 1), (24809, 4), (24809, 8), (24809, 16), (24808, 1)) if want("dense") else ():
         T = torch.rand((rows, rows), dtype=torch.float64, device="cuda")
         c = torch.rand((rows, k), dtype=torch.float64, device="cuda")
         o = torch.empty((rows, k), dtype=torch.float64, device="cuda")
@@ -73,7 +83,7 @@ def main():
         def run():
             _lib.check(lib.mpx_apply_dense(0, T.data_ptr(), rows, rows, rows, c.data_ptr(), k, k,
                                            o.data_ptr(), k, stream))
-        ms = timed(run)
+        ms = timed(run, args.iters)
         gbs = rows * rows * 8 / (ms * 1e-3) / 1e9
         ref = (T[:64] @ c)
         err = ((o[:64] - ref).abs().max() / ref.abs().max()).item()
