@@ -274,6 +274,13 @@ class DDSOperator:
             self._full = api.dds(np.eye(len(self.grid.multi_index)), self.grid.tree)
         return self._full
 
+    def full_on_device(self, device=None):
+        """The same matrix as a CUDA tensor: identity built and transformed on the device."""
+        import torch
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        return api.dds(torch.eye(len(self.grid.multi_index), dtype=torch.float64, device=dev),
+                       self.grid.tree)
+
 
 class NodeEvalOperator:
     """Newton -> Lagrange as an operator: evaluation at the unisolvent nodes."""

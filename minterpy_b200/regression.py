@@ -31,10 +31,13 @@ def compute_regression_matrix(basis_poly, xx):
     e = basis_poly.multi_index.exponents
     gp = basis_poly.grid.generating_points
     if isinstance(basis_poly, LagrangePolynomial):
-        l2n = LagrangeToNewton(basis_poly).transformation_operator.array_repr_full
+        op = LagrangeToNewton(basis_poly).transformation_operator
         if _is_torch(xx):
-            import torch
-            l2n = torch.as_tensor(l2n, device=xx.device)
+            # the N x N Lagrange->Newton matrix never visits the host: identity and dds on
+            # the device, then evaluation with k = N coefficient columns
+            l2n = op.full_on_device(xx.device)
+        else:
+            l2n = op.array_repr_full
         rr = api.eval_newton_polynomials(xx, l2n, e, gp)
         # the reference's two edge cases: a single point, a single basis function
         if xx.shape[0] == 1:
