@@ -90,7 +90,7 @@ struct T1Layout {
 // K is a compile-time constant, so the body is straight-line code: K broadcast loads of
 // coefficient pairs, the T1 values of the R points, 2K FMAs per point into A independent
 // accumulators (A = 2: odd and even monomials apart), then one FMA per point into the
-// level-1 sum.  Highest monomial first.
+// level-1 sum.  Lowest monomial first.
 template <int L0P, int R, int A, int NT, int K>
 __device__ __forceinline__ void run_leaves(double (&acc1)[R], const double (&T0)[R][L0P],
                                            uint32_t &cp, uint32_t &t1a, int cnt)
@@ -103,22 +103,24 @@ __device__ __forceinline__ void run_leaves(double (&acc1)[R], const double (&T0)
         for (int i = 0; i < K; ++i) cf[i] = lds128(cp + 16 * i);
         double t1v[R];
         T1Layout<R, NT>::load(t1v, t1a);
+        // T0[.][0] is 1: the coefficient of exponent 0 enters as the addend of the first FMA,
+        // so a leaf of 2K monomials costs 2K - 1 FP64 operations (plus the level-1 FMA)
         double a[R][A];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             if constexpr (A == 2) {
-                a[r][1] = cf[K - 1].y * T0[r][2 * K - 1];
-                a[r][0] = cf[K - 1].x * T0[r][2 * K - 2];
+                a[r][1] = cf[0].y * T0[r][1];
+                a[r][0] = cf[0].x;
             } else {
-                a[r][0] = fma(cf[K - 1].x, T0[r][2 * K - 2], cf[K - 1].y * T0[r][2 * K - 1]);
+                a[r][0] = fma(cf[0].y, T0[r][1], cf[0].x);
             }
         }
 #pragma unroll
-        for (int i = K - 2; i >= 0; --i) {
+        for (int i = 1; i < K; ++i) {
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                a[r][A - 1] = fma(cf[i].y, T0[r][2 * i + 1], a[r][A - 1]);
                 a[r][0] = fma(cf[i].x, T0[r][2 * i], a[r][0]);
+                a[r][A - 1] = fma(cf[i].y, T0[r][2 * i + 1], a[r][A - 1]);
             }
         }
 #pragma unroll

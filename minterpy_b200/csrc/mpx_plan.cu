@@ -177,7 +177,7 @@ int compile_program(const int64_t *e, int64_t N, int m, const std::vector<int64_
             slots[e[row * m]] = (int32_t)row;
         }
         coef_used += lenp;
-        pg.fma_per_point += lenp + 1 + nf;
+        pg.fma_per_point += lenp + nf;      // lenp - 1 in the leaf sum, 1 into level 1
         // a leaf that folds or ends the program closes its record and hands it its tail
         if (nf > 0 || last) {
             hdr |= tail;

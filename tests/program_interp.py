@@ -73,8 +73,8 @@ def run_program(desc, slots, x, coeffs, exponents, gp):
             for K in range(l0p // 2, 0, -1):           # lengths walk downwards
                 cnt = (counts[(K - 1) // 8] >> (4 * ((K - 1) % 8))) & 15
                 for _ in range(cnt):
-                    a = 0.0
-                    for s in range(2 * K - 1, -1, -1):
+                    a = packed[cp]                     # T0[0] = 1: enters as an addend
+                    for s in range(1, 2 * K):
                         a += packed[cp + s] * T0[s]
                         fma += 1
                     cp += 2 * K
