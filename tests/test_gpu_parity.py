@@ -423,3 +423,42 @@ def test_large_properties_other_configs(mpb, golden_cfg, tag, P, k):
     idx = torch.randint(0, P, (24,), generator=gen, device="cuda")
     ref = oracle.eval_newton_polynomials(xx[idx].cpu().numpy(), c1.cpu().numpy(), e, gp, nthreads=4)
     assert rel_err(y1[idx].cpu().numpy(), ref) <= EVAL_RTOL
+
+
+def test_concurrent_host_threads(mpb, golden_cfg):
+    """ctypes releases the GIL during the foreign call, so Python threads really do enter the
+    library at once (SURVEY.md 8b "Threading"): several threads on ONE plan (serialised by the
+    plan's mutex: staging buffers and packed coefficients are per plan) and threads on
+    different plans (independent) must all get the single-threaded answers, bit for bit."""
+    import threading
+    g2, g5 = golden_cfg("cfg2"), golden_cfg("cfg5")
+    plans = [mpb.get_plan(g2["exponents"], g2["generating_points"]),
+             mpb.get_plan(g5["exponents"], g5["generating_points"])]
+    rng = np.random.default_rng(77)
+    jobs = []
+    for t in range(8):
+        plan = plans[t % 2] if t < 4 else plans[0]
+        xx = rng.uniform(-1, 1, (3000 + 511 * t, plan.m))
+        c = rng.uniform(-1, 1, (plan.N, 1 + t % 3))
+        v = rng.uniform(-1, 1, (plan.N, 2))
+        jobs.append((plan, xx, c, v))
+    want = [(p.eval(xx, c), p.dds(v)) for p, xx, c, v in jobs]
+    got = [None] * len(jobs)
+    errors = []
+
+    def work(i):
+        try:
+            p, xx, c, v = jobs[i]
+            for _ in range(3):
+                got[i] = (p.eval(xx, c), p.dds(v))
+        except Exception as ex:       # noqa: BLE001
+            errors.append(ex)
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(len(jobs))]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    for (we, wd), (ge, gd) in zip(want, got):
+        assert np.array_equal(we, ge) and np.array_equal(wd, gd)
