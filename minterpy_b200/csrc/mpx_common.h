@@ -83,6 +83,12 @@ struct DdsDim {
     int32_t *d_off = nullptr;   // n_fibers + 1
     int32_t *d_rows = nullptr;  // N, rows grouped by fiber, in order of increasing exponent
     double *d_diff = nullptr;   // (L x L) table: diff[l*L + r] = gp[r,d] - gp[l,d], L = max_len
+    // work list of the one-warp-per-fiber kernel: fibers with at least 2 elements, longest first
+    int n_work = 0;
+    int32_t *d_woff = nullptr;  // n_work + 1
+    int32_t *d_wrows = nullptr; // rows of those fibers
+    double *d_dy = nullptr;     // (L x L) pairs (divisor, reciprocal or 0), 2 doubles each
+    double *d_gcol = nullptr;   // (L) generating points of this dimension
 };
 
 // A group of consecutive dimensions [lo, hi] that the divided-difference kernel handles in
@@ -154,6 +160,21 @@ int mpx_fail(int code, const std::string &msg);
         if (_e != cudaSuccess)                                                             \
             return mpx_fail(MPX_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
     } while (0)
+
+// Dynamic shared memory limit of a kernel: always raised to the device's opt-in maximum, never
+// to the size of one launch.  The attribute belongs to the function, process-wide, so two host
+// threads launching the same kernel with different sizes (two plans) would otherwise race: one
+// lowers the limit between the other's set and launch.
+template <typename F>
+inline cudaError_t mpx_allow_max_smem(F fn)
+{
+    int device = 0, smem_max = 0;
+    cudaError_t e = cudaGetDevice(&device);            // the entry points select the plan's device
+    if (e != cudaSuccess) return e;
+    e = cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+}
 
 struct DeviceGuard {
     int prev = -1;

@@ -9,7 +9,9 @@
 // bit-identical: true division, no FMA contraction possible in (a-b)/c.
 // One thread owns one (fiber, column) pair and keeps the fiber in registers; the k value
 // columns are the fastest thread index, so global accesses are coalesced along a row.
+#include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 #include "mpx_common.h"
 
@@ -265,7 +267,183 @@ dds_group_kernel(double *__restrict__ vals, int64_t ld, int k, const DdsGroupArg
             vals[(int64_t)g.slice_rows[r0 + r] * ld + col] = v[(size_t)r * MPX_DDS_COLS + lane];
 }
 
+// ---- one warp per fiber, one pass per dimension ------------------------------------------
+// A warp gathers ONE fiber (len rows x 32 value columns) into its private piece of shared
+// memory, runs the 1-D scheme there with direct addressing (row r of the fiber is row r of the
+// buffer), and writes rows 1..len-1 back.  No lane ever touches another lane's column, so the
+// kernel has no barrier after the table is staged: warps come and go independently and the
+// gather latency of one hides behind the arithmetic of the others -- where the fused kernel
+// above spends 40 % of its warp time at barriers and on its gather.  The price is one read and
+// one write of the value array per dimension instead of one per dimension group.
+
+template <bool FAST, int FW>
+__global__ void __launch_bounds__(FW * 32)
+dds_fiber_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_t *__restrict__ woff,
+                 const int32_t *__restrict__ wrows, int n_work, const double *__restrict__ dy,
+                 const double *__restrict__ gcol, int L)
+{
+    extern __shared__ __align__(16) unsigned char fsm[];
+    // FAST: (divisor, reciprocal) pairs, L*L of them; else the L generating points
+    double *tab = reinterpret_cast<double *>(fsm);
+    const int tab_doubles = FAST ? 2 * L * L : ((L + 1) & ~1);
+    if constexpr (FAST) {
+        for (int i = threadIdx.x; i < 2 * L * L; i += blockDim.x) tab[i] = dy[i];
+    } else {
+        for (int i = threadIdx.x; i < L; i += blockDim.x) tab[i] = gcol[i];
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int f = blockIdx.x * FW + warp;
+    const int col = blockIdx.y * MPX_DDS_COLS + lane;
+    if (f >= n_work || col >= k) return;
+    const int o = woff[f];
+    const int len = woff[f + 1] - o;
+    double *b = tab + tab_doubles + (size_t)warp * L * MPX_DDS_COLS + lane;     // b[r * 32]
+    const int32_t *rows = wrows + o;
+    // (fetching the row numbers once per warp and handing them round by shuffles was measured:
+    // no gain, the index loads hit L1)
+    {
+        int r = 0;
+        for (; r + 3 < len; r += 4) {                 // four row segments in flight
+            double x[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) x[q] = vals[(int64_t)rows[r + q] * ld + col];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) b[(r + q) * MPX_DDS_COLS] = x[q];
+        }
+        for (; r < len; ++r) b[r * MPX_DDS_COLS] = vals[(int64_t)rows[r] * ld + col];
+    }
+    if constexpr (FAST) {
+        // Row-blocked sweep.  Element r receives its updates i = 1..r in order, each using the
+        // FINAL value of element i-1, so the rows can be finished one after the other (the same
+        // operations on every element as the column-wise order of the reference).  Four rows
+        // advance together: they share the read of v[i-1], their four (divisor, reciprocal)
+        // pairs are neighbours in the table, and the running values stay in registers -- no
+        // store per update, no remainder loop per step.  The last three updates of rows
+        // r+1..r+3 use the rows of the block itself.
+        const double2 *dy2 = reinterpret_cast<const double2 *>(tab);
+        // the (len - 1) % 4 rows that do not fill a block are the FIRST ones: their chains are
+        // the shortest
+        int r = 1;
+        const int first_block = 1 + ((len - 1) & 3);
+        for (; r < first_block; ++r) {
+            double x = b[r * MPX_DDS_COLS];
+            const double2 *t = dy2 + r;
+            const double *vp = b;
+#pragma unroll 1
+            for (int i = 1; i <= r; ++i) {
+                const double2 t0 = t[0];
+                x = dds_update<true>(x, *vp, t0.x, t0.y);
+                t += L;
+                vp += MPX_DDS_COLS;
+            }
+            b[r * MPX_DDS_COLS] = x;
+        }
+        for (; r + 3 < len; r += 4) {
+            double *p = b + r * MPX_DDS_COLS;
+            double x0 = p[0], x1 = p[MPX_DDS_COLS], x2 = p[2 * MPX_DDS_COLS], x3 = p[3 * MPX_DDS_COLS];
+            const double2 *t = dy2 + r;               // entries (i-1, r..r+3), i-1 = 0
+            const double *vp = b;
+#pragma unroll 1
+            for (int i = 1; i <= r; ++i) {
+                const double pv = *vp;
+                const double2 t0 = t[0], t1 = t[1], t2 = t[2], t3 = t[3];
+                x0 = dds_update<true>(x0, pv, t0.x, t0.y);
+                x1 = dds_update<true>(x1, pv, t1.x, t1.y);
+                x2 = dds_update<true>(x2, pv, t2.x, t2.y);
+                x3 = dds_update<true>(x3, pv, t3.x, t3.y);
+                t += L;
+                vp += MPX_DDS_COLS;
+            }
+            {
+                const double2 t1 = t[1], t2 = t[2], t3 = t[3];          // table row r
+                x1 = dds_update<true>(x1, x0, t1.x, t1.y);
+                x2 = dds_update<true>(x2, x0, t2.x, t2.y);
+                x3 = dds_update<true>(x3, x0, t3.x, t3.y);
+                t += L;
+                const double2 u2 = t[2], u3 = t[3];                      // table row r + 1
+                x2 = dds_update<true>(x2, x1, u2.x, u2.y);
+                x3 = dds_update<true>(x3, x1, u3.x, u3.y);
+                t += L;
+                const double2 w3 = t[3];                                 // table row r + 2
+                x3 = dds_update<true>(x3, x2, w3.x, w3.y);
+            }
+            p[0] = x0;
+            p[MPX_DDS_COLS] = x1;
+            p[2 * MPX_DDS_COLS] = x2;
+            p[3 * MPX_DDS_COLS] = x3;
+        }
+    } else {
+        for (int i = 1; i < len; ++i) {
+            const double pv = b[(i - 1) * MPX_DDS_COLS];
+            const double gl = tab[i - 1];
+            int r = i;
+            for (; r + 1 < len; r += 2) {
+                double *p = b + r * MPX_DDS_COLS;
+                const double x0 = p[0], x1 = p[MPX_DDS_COLS];
+                const double y0 = dds_update<false>(x0, pv, __dsub_rn(tab[r], gl), 0.0);
+                const double y1 = dds_update<false>(x1, pv, __dsub_rn(tab[r + 1], gl), 0.0);
+                p[0] = y0;
+                p[MPX_DDS_COLS] = y1;
+            }
+            for (; r < len; ++r)
+                b[r * MPX_DDS_COLS] = dds_update<false>(b[r * MPX_DDS_COLS], pv, __dsub_rn(tab[r], gl), 0.0);
+        }
+    }
+    for (int r = 1; r < len; ++r)                      // element 0 of a fiber never changes
+        vals[(int64_t)rows[r] * ld + col] = b[r * MPX_DDS_COLS];
+}
+
 }  // namespace
+
+template <int FW>
+static int launch_dds_fibers_fw(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
+                                bool *handled)
+{
+    static const bool force_div = getenv("MPX_DDS_TRUE_DIV") != nullptr;
+    int smem_max = 0;
+    MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
+    *handled = false;
+    auto smem_of = [&](const DdsDim &dd, bool fast) {
+        return ((fast ? (size_t)2 * dd.max_len * dd.max_len : (size_t)((dd.max_len + 1) & ~1)) +
+                (size_t)FW * dd.max_len * MPX_DDS_COLS) * sizeof(double);
+    };
+    // every dimension must fit before anything is launched (no half-transformed arrays)
+    for (int d = 0; d < pl->m; ++d) {
+        const DdsDim &dd = pl->dds[d];
+        if (dd.n_work == 0) continue;
+        const bool fast = dd.max_len <= 40 && !force_div;
+        if (smem_of(dd, fast) > (size_t)smem_max || dd.max_len > DDS_MAX_FIBER) return MPX_OK;
+    }
+    for (int d = pl->m - 1; d >= 0; --d) {
+        const DdsDim &dd = pl->dds[d];
+        if (dd.n_work == 0) continue;
+        const bool fast = dd.max_len <= 40 && !force_div;
+        const size_t smem = smem_of(dd, fast);
+        auto fn = fast ? dds_fiber_kernel<true, FW> : dds_fiber_kernel<false, FW>;
+        MPX_CUDA(mpx_allow_max_smem(fn));
+        dim3 grid((unsigned)((dd.n_work + FW - 1) / FW), (unsigned)((k + MPX_DDS_COLS - 1) / MPX_DDS_COLS), 1);
+        fn<<<grid, FW * 32, smem, stream>>>(vals, ld, k, dd.d_woff, dd.d_wrows, dd.n_work, dd.d_dy,
+                                            dd.d_gcol, dd.max_len);
+        MPX_CUDA(cudaGetLastError());
+    }
+    *handled = true;
+    return MPX_OK;
+}
+
+static int launch_dds_fibers(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
+                             bool *handled)
+{
+    // warps per CTA: short fibers leave room for many small CTAs (more resident warps, measured
+    // 7 % faster at cfg4); long fibers want fewer, larger buffers per CTA
+    int longest = 0;
+    for (int d = 0; d < pl->m; ++d) longest = std::max(longest, pl->dds[d].max_len);
+    static const int forced = getenv("MPX_DDS_FIBER_WARPS") ? atoi(getenv("MPX_DDS_FIBER_WARPS")) : 0;
+    const int fw = forced ? forced : (longest <= 16 || longest > 64) ? 4 : 8;
+    if (fw == 4) return launch_dds_fibers_fw<4>(pl, vals, k, ld, stream, handled);
+    if (fw == 16) return launch_dds_fibers_fw<16>(pl, vals, k, ld, stream, handled);
+    return launch_dds_fibers_fw<8>(pl, vals, k, ld, stream, handled);
+}
 
 static int launch_dds_per_dim(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream)
 {
@@ -300,6 +478,14 @@ int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t s
                         "indices, but DDS only works for complete multi indices (without 'holes').");
     static const bool per_dim = getenv("MPX_DDS_PER_DIM") != nullptr;   // old one-pass-per-dimension path
     if (per_dim) return launch_dds_per_dim(pl, vals, k, ld, stream);
+    // default: one warp per fiber, one pass per dimension; MPX_DDS_MODE=group selects the fused
+    // slice kernel, which also takes over when a fiber buffer does not fit shared memory
+    static const char *mode = getenv("MPX_DDS_MODE");          // "fiber" | "group"
+    if (!mode || strcmp(mode, "group") != 0) {
+        bool handled = false;
+        int rc = launch_dds_fibers(pl, vals, k, ld, stream, &handled);
+        if (rc != MPX_OK || handled) return rc;
+    }
     for (const DdsGroup &grp : pl->dds_groups) {
         DdsGroupArgs a;
         a.slice_off = grp.d_slice_off;
@@ -328,7 +514,7 @@ int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t s
         MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
         if (smem > (size_t)smem_max) return mpx_fail(MPX_ERR_UNSUPPORTED, "dds slice does not fit shared memory");
         auto fn = fast ? dds_group_kernel<true> : dds_group_kernel<false>;
-        MPX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MPX_CUDA(mpx_allow_max_smem(fn));
         dim3 grid((unsigned)grp.n_slices, (unsigned)((k + MPX_DDS_COLS - 1) / MPX_DDS_COLS), 1);
         fn<<<grid, DDS_WARPS * 32, smem, stream>>>(vals, ld, k, a);
         MPX_CUDA(cudaGetLastError());

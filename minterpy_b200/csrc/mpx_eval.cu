@@ -529,7 +529,7 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
     prm.n_chunks = pl->prog.n_chunks; prm.stages = stages; prm.m = pl->m; prm.gp_rows = pl->gp_rows;
     for (int i = 0; i < MPX_MAX_M; ++i) { prm.max_exp[i] = pl->max_exp[i]; prm.start_exp[i] = pl->start_exp[i]; }
 
-    MPX_CUDA(cudaFuncSetAttribute(v->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MPX_CUDA(mpx_allow_max_smem(v->fn));
     const int64_t per_cta = (int64_t)v->r * nt;
     const int64_t tiles = (P + per_cta - 1) / per_cta;
     if (tiles > 0x7fffffffLL || k > 65535)

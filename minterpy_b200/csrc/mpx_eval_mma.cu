@@ -242,7 +242,7 @@ template <int NT8, int NW, int MP>
 int launch_variant(const MmaParams &prm, int tiles, size_t smem, cudaStream_t stream)
 {
     auto fn = &eval_mma_kernel<NT8, NW, MP>;
-    MPX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MPX_CUDA(mpx_allow_max_smem(fn));
     const int64_t ptiles = (prm.P + 32 * NW - 1) / (32 * NW);
     if (ptiles > 0x7fffffffLL || tiles > 65535)
         return mpx_fail(MPX_ERR_UNSUPPORTED, "too many points or polynomials for one launch");

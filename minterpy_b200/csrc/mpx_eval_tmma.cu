@@ -312,7 +312,7 @@ template <int KS0, int NW, int MT, int MINB>
 int launch_tmma(const TmmaParams &prm, int k, size_t smem, cudaStream_t stream)
 {
     auto fn = &eval_tmma_kernel<KS0, NW, MT, MINB>;
-    MPX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MPX_CUDA(mpx_allow_max_smem(fn));
     const int64_t ptiles = (prm.P + 8 * MT * NW - 1) / (8 * MT * NW);
     if (ptiles > 0x7fffffffLL || k > 65535)
         return mpx_fail(MPX_ERR_UNSUPPORTED, "too many points or polynomials for one launch");

@@ -138,11 +138,11 @@ void launch_m(bool tri, dim3 grid, size_t smem, cudaStream_t st, const double *x
               int64_t P, const mpx_plan *pl, double *out, int64_t ld_out, int64_t n_per_cta)
 {
     if (tri) {
-        cudaFuncSetAttribute(monomials_kernel<M, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        mpx_allow_max_smem(monomials_kernel<M, true>);
         monomials_kernel<M, true><<<grid, 256, smem, st>>>(xx, ld_xx, P, pl->d_exp64, pl->N, pl->d_gp,
                                                           pl->gp_rows, pl->d_max_exp, out, ld_out, n_per_cta);
     } else {
-        cudaFuncSetAttribute(monomials_kernel<M, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        mpx_allow_max_smem(monomials_kernel<M, false>);
         monomials_kernel<M, false><<<grid, 256, smem, st>>>(xx, ld_xx, P, pl->d_exp64, pl->N, pl->d_gp,
                                                            pl->gp_rows, pl->d_max_exp, out, ld_out, n_per_cta);
     }
@@ -180,8 +180,7 @@ int mpx_launch_monomials(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_x
         default: launch_m<8>(tri, grid, smem, stream, xx, ld_xx, P, pl, out, ld_out, n_per_cta); break;
         }
     } else {
-        MPX_CUDA(cudaFuncSetAttribute(monomials_generic_kernel,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MPX_CUDA(mpx_allow_max_smem(monomials_generic_kernel));
         monomials_generic_kernel<<<grid, 256, smem, stream>>>(xx, ld_xx, P, pl->d_exp8, pl->N, pl->m,
                                                              pl->d_gp, pl->gp_rows, pl->d_max_exp,
                                                              out, ld_out, triangular, n_per_cta);

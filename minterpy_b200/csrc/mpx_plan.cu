@@ -39,6 +39,20 @@ struct LexLess {
     }
 };
 
+// The reciprocal + one correction division (mpx_dds.cu) returns the IEEE quotient only for
+// ordinary divisors: moderate exponent, significand not all ones (e.g. 1 - 6e-17 between
+// Chebyshev points DOES occur).  Others get reciprocal 0, which sends the kernel to the true
+// division.
+double reciprocal_or_zero(double dv)
+{
+    uint64_t bits;
+    std::memcpy(&bits, &dv, 8);
+    const int ex = (int)((bits >> 52) & 0x7ff);
+    const uint64_t mant = bits & 0xfffffffffffffull;
+    const bool ordinary = ex >= 1023 - 200 && ex <= 1023 + 200 && mant != 0xfffffffffffffull;
+    return ordinary ? 1.0 / dv : 0.0;      // host division: RN(1/d)
+}
+
 int64_t find_sorted(const int64_t *e, const std::vector<int64_t> &order, int m,
                     const int64_t *key)
 {
@@ -416,17 +430,7 @@ int build_dds_groups(mpx_plan *pl, const int64_t *e, const std::vector<std::vect
                     if (r != l) {
                         const double dv = gp_h[(size_t)r * m + d] - gp_h[(size_t)l * m + d];
                         diff[(size_t)l * L + r] = dv;
-                        // The reciprocal + one correction division returns the IEEE quotient
-                        // only for ordinary divisors: moderate exponent, significand not all
-                        // ones (e.g. 1 - 6e-17 between Chebyshev points DOES occur).  Others
-                        // get reciprocal 0, which sends the kernel to the true division.
-                        uint64_t bits;
-                        std::memcpy(&bits, &dv, 8);
-                        const int ex = (int)((bits >> 52) & 0x7ff);
-                        const uint64_t mant = bits & 0xfffffffffffffull;
-                        const bool ordinary = ex >= 1023 - 200 && ex <= 1023 + 200 &&
-                                              mant != 0xfffffffffffffull;
-                        recip[(size_t)l * L + r] = ordinary ? 1.0 / dv : 0.0;   // host division: RN(1/d)
+                        recip[(size_t)l * L + r] = reciprocal_or_zero(dv);
                     }
             DdsGroupDim gd;
             gd.dim = d;
@@ -594,6 +598,40 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
             if ((rc = upload(&dd.d_off, off)) != MPX_OK) return rc;
             if ((rc = upload(&dd.d_rows, rows)) != MPX_OK) return rc;
             if ((rc = upload(&dd.d_diff, diff)) != MPX_OK) return rc;
+            {
+                // work list: fibers with something to do, longest first (the tail of the launch
+                // is then made of short fibers)
+                const int nfib = dd.n_fibers;
+                std::vector<int> byl(nfib);
+                std::iota(byl.begin(), byl.end(), 0);
+                std::stable_sort(byl.begin(), byl.end(), [&](int a, int b) {
+                    return off[a + 1] - off[a] > off[b + 1] - off[b];
+                });
+                std::vector<int32_t> woff, wrows;
+                for (int f : byl) {
+                    const int len = off[f + 1] - off[f];
+                    if (len < 2) break;
+                    woff.push_back((int32_t)wrows.size());
+                    wrows.insert(wrows.end(), rows.begin() + off[f], rows.begin() + off[f + 1]);
+                }
+                dd.n_work = (int)woff.size();
+                woff.push_back((int32_t)wrows.size());
+                if (wrows.empty()) wrows.push_back(0);
+                std::vector<double> dy((size_t)2 * max_len * max_len, 1.0), gcol(max_len);
+                for (int l = 0; l < max_len; ++l) {
+                    gcol[l] = gp_h[(size_t)l * m + d];
+                    for (int r = 0; r < max_len; ++r)
+                        if (r != l) {
+                            const double dv = diff[(size_t)l * max_len + r];
+                            dy[2 * ((size_t)l * max_len + r)] = dv;
+                            dy[2 * ((size_t)l * max_len + r) + 1] = reciprocal_or_zero(dv);
+                        }
+                }
+                if ((rc = upload(&dd.d_woff, woff)) != MPX_OK) return rc;
+                if ((rc = upload(&dd.d_wrows, wrows)) != MPX_OK) return rc;
+                if ((rc = upload(&dd.d_dy, dy)) != MPX_OK) return rc;
+                if ((rc = upload(&dd.d_gcol, gcol)) != MPX_OK) return rc;
+            }
             fibers_off[d] = std::move(off);
             fibers_rows[d] = std::move(rows);
         }
@@ -640,6 +678,10 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
         cudaFree(dd.d_off);
         cudaFree(dd.d_rows);
         cudaFree(dd.d_diff);
+        cudaFree(dd.d_woff);
+        cudaFree(dd.d_wrows);
+        cudaFree(dd.d_dy);
+        cudaFree(dd.d_gcol);
     }
     delete pl;
 }

@@ -442,15 +442,17 @@ def test_concurrent_host_threads(mpb, golden_cfg):
         c = rng.uniform(-1, 1, (plan.N, 1 + t % 3))
         v = rng.uniform(-1, 1, (plan.N, 2))
         jobs.append((plan, xx, c, v))
-    want = [(p.eval(xx, c), p.dds(v)) for p, xx, c, v in jobs]
+    want = [(p.eval(xx, c), p.dds(v), p.monomials(xx[:64])) for p, xx, c, v in jobs]
     got = [None] * len(jobs)
     errors = []
 
     def work(i):
+        # the two plans launch the same kernels with different shared-memory sizes: a
+        # per-launch function attribute would race here (it did, once in five runs)
         try:
             p, xx, c, v = jobs[i]
-            for _ in range(3):
-                got[i] = (p.eval(xx, c), p.dds(v))
+            for _ in range(6):
+                got[i] = (p.eval(xx, c), p.dds(v), p.monomials(xx[:64]))
         except Exception as ex:       # noqa: BLE001
             errors.append(ex)
 
@@ -460,5 +462,39 @@ def test_concurrent_host_threads(mpb, golden_cfg):
     for th in threads:
         th.join()
     assert not errors, errors
-    for (we, wd), (ge, gd) in zip(want, got):
-        assert np.array_equal(we, ge) and np.array_equal(wd, gd)
+    for (we, wd, wm), (ge, gd, gm) in zip(want, got):
+        assert np.array_equal(we, ge) and np.array_equal(wd, gd) and np.array_equal(wm, gm)
+
+
+def test_dds_fused_slice_kernel_still_bit_exact():
+    """The default dds path is one warp per fiber; the fused slice kernel stays as the fallback
+    for fibers whose buffers do not fit shared memory (MPX_DDS_MODE=group selects it, read once
+    per process -- hence a child process).  Same goldens, same bit-exact bar."""
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import sys
+sys.path.insert(0, "tests"); sys.path.insert(0, "tests/golden")
+import numpy as np, golden_io, minterpy_b200 as mpb
+small = golden_io.load("small")
+n = 0
+for tag in sorted({k.split("/")[0] for k in small}):
+    plan = mpb.get_plan(small[f"{tag}/exponents"], small[f"{tag}/generating_points"])
+    for k in (1, 10):
+        assert np.array_equal(plan.dds(small[f"{tag}/k{k}/dds_in"]), small[f"{tag}/k{k}/dds_ref"]), tag
+        n += 1
+for tag in ("cfg2", "cfg3", "cfg4", "cfg5"):
+    g = golden_io.load(tag)
+    e, gp = g["exponents"], g["generating_points"]
+    vals = golden_io.seeded(g, "dds_seed", "dds_in_sha", g["dds_ref"].shape)
+    assert np.array_equal(mpb.get_plan(e, gp).dds(vals), g["dds_ref"]), tag
+    n += 1
+print("OK", n)
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, MPX_DDS_MODE="group")
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True,
+                         text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert out.stdout.strip().startswith("OK 76")
