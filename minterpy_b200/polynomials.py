@@ -308,13 +308,71 @@ class NodeEvalOperator:
                                                    self.grid.generating_points, triangular=True)
         return self._full
 
+    def full_on_device(self, device=None):
+        """The same matrix as a CUDA tensor."""
+        import torch
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        return api.eval_newton_monomials(torch.as_tensor(self.grid.unisolvent_nodes, device=dev),
+                                         self.grid.multi_index.exponents,
+                                         self.grid.generating_points, triangular=True)
+
+
+class MatrixOperator:
+    """A dense operator (``schemes/matrix_operator.py:10-26``): ``op @ coeffs`` is one pass of
+    ``mpx_apply_dense`` over the matrix, which stays on the device; ``op @ op`` gives the
+    operator of the matrix product."""
+
+    def __init__(self, matrix):
+        self._host = None if _is_torch(matrix) else np.ascontiguousarray(matrix, dtype=np.float64)
+        self._dev = matrix.contiguous() if _is_torch(matrix) else None
+
+    def _on_device(self):
+        if self._dev is None:
+            import torch
+            self._dev = torch.as_tensor(self._host, device="cuda")
+        return self._dev
+
+    @property
+    def array_repr_full(self):
+        if self._host is None:
+            self._host = self._dev.cpu().numpy()
+        return self._host
+
+    def __matmul__(self, other):
+        if isinstance(other, (MatrixOperator, DDSOperator, NodeEvalOperator)):
+            return MatrixOperator(self.array_repr_full @ other.array_repr_full)
+        import torch
+        T = self._on_device()
+        as_numpy = not _is_torch(other)
+        c = torch.as_tensor(np.ascontiguousarray(other, dtype=np.float64) if as_numpy else other,
+                            dtype=torch.float64, device=T.device)
+        if c.shape[0] != T.shape[1]:
+            raise ValueError(f"operator of shape {tuple(T.shape)} cannot be applied to "
+                             f"{c.shape[0]} coefficients")
+        c2 = (c.reshape(-1, 1) if c.ndim == 1 else c).contiguous()
+        out = torch.empty((T.shape[0], c2.shape[1]), dtype=torch.float64, device=T.device)
+        stream = torch.cuda.current_stream(T.device).cuda_stream
+        check(lib().mpx_apply_dense(T.device.index, T.data_ptr(), T.shape[0], T.shape[1], T.stride(0),
+                                    c2.data_ptr(), c2.shape[1], c2.stride(0), out.data_ptr(),
+                                    out.stride(0), stream))
+        if c.ndim == 1:
+            out = out.reshape(-1)
+        return out.cpu().numpy() if as_numpy else out
+
 
 class LagrangeToNewton(_Transformation):
     origin_type = LagrangePolynomial
     target_type = NewtonPolynomial
 
     def _get_transformation_operator(self):
-        return DDSOperator(self.grid)
+        """Divided differences where the index set is complete; otherwise, like the reference
+        (``transformations/utils.py:155-179``), the dense inverse of the Newton->Lagrange matrix
+        (the monomials at the unisolvent nodes), built and inverted on the device."""
+        if self.grid.multi_index.is_complete:
+            return DDSOperator(self.grid)
+        import torch
+        n2l = NodeEvalOperator(self.grid).full_on_device()
+        return MatrixOperator(torch.linalg.inv(n2l))
 
 
 class NewtonToLagrange(_Transformation):

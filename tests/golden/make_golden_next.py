@@ -10,6 +10,8 @@ Writes tests/golden/next_rows.npz:
 * ``reg/*``     ``OrdinaryRegression`` in the Lagrange and Newton bases: regression matrix,
                 coefficients, error measures, predictions
 * ``ari/*``     ``LagrangePolynomial`` ``+ - *``
+* ``inc/*``     ``LagrangeToNewton`` on index sets WITH holes: the reference falls back to a dense
+                ``MatrixOperator`` holding ``inv(N2L)`` (``transformations/utils.py:155-179``)
 """
 import os
 import sys
@@ -145,6 +147,32 @@ for (m, (n1, lp1), (n2, lp2)) in [(1, (3, 2.0), (5, 2.0)), (2, (3, 1.0), (2, 2.0
         out[f"ari/{ari_n}/{name}/coeffs_ref"] = res.coeffs
     ari_n += 1
 out["ari/count"] = np.int64(ari_n)
+
+# ---- incomplete index sets: dense operator ------------------------------------------------------
+rng = np.random.default_rng(815)
+inc_n = 0
+for (m, n, lp, drop) in [(2, 3, 2.0, [4]), (2, 4, 1.0, [2, 7]), (3, 3, 2.0, [5, 11]),
+                         (3, 2, np.inf, [13]), (2, 12, 2.0, [30, 31, 77])]:
+    full = mp.MultiIndexSet.from_degree(m, n, lp).exponents
+    mi = mp.MultiIndexSet(np.delete(full, drop, axis=0), lp_degree=lp)
+    assert not mi.is_complete
+    grid = mp.Grid(mi)
+    N = len(mi)
+    c1 = rng.uniform(-1, 1, N)
+    c3 = rng.uniform(-1, 1, (N, 3))
+    trafo = mp.LagrangeToNewton(mp.LagrangePolynomial(mi, c1, grid=grid))
+    assert type(trafo.transformation_operator).__name__ == "MatrixOperator"
+    out[f"inc/{inc_n}/exponents"] = mi.exponents.astype(np.uint8)
+    out[f"inc/{inc_n}/lp"] = np.float64(lp)
+    out[f"inc/{inc_n}/generating_points"] = grid.generating_points
+    out[f"inc/{inc_n}/coeffs1"] = c1
+    out[f"inc/{inc_n}/coeffs3"] = c3
+    out[f"inc/{inc_n}/operator_ref"] = trafo.transformation_operator.array_repr_full
+    out[f"inc/{inc_n}/l2n1_ref"] = trafo().coeffs
+    out[f"inc/{inc_n}/l2n3_ref"] = mp.LagrangeToNewton(
+        mp.LagrangePolynomial(mi, c3, grid=grid))().coeffs
+    inc_n += 1
+out["inc/count"] = np.int64(inc_n)
 
 path = os.path.join(HERE, "next_rows.npz")
 np.savez_compressed(path, **out)

@@ -268,3 +268,51 @@ def test_interpolate_with_the_reference_signature(mpb, golden_cfg):
     assert np.array_equal(poly.coeffs, g["quickstart_coeffs"])
     yq = poly(np.linspace(-1, 1, 1_000_000))
     assert rel_err(yq[::1000], g["quickstart_every1000"]) <= 1e-13
+
+
+# ---- incomplete index sets: dense operator ------------------------------------------------------
+def test_lagrange_to_newton_on_sets_with_holes(mpb, nxt):
+    """transformations/utils.py:155-179: without completeness there are no divided differences;
+    the operator is the dense inverse of the Newton->Lagrange matrix, applied by mpx_apply_dense.
+    Inversion is LAPACK on the reference's side and cuSOLVER here: 1e-10 * max|ref|."""
+    from minterpy_b200.polynomials import MatrixOperator
+    assert int(nxt["inc/count"]) >= 5
+    for i in range(int(nxt["inc/count"])):
+        e, gp = nxt[f"inc/{i}/exponents"], nxt[f"inc/{i}/generating_points"]
+        mi = mpb.MultiIndexSet(e, lp_degree=float(nxt[f"inc/{i}/lp"]))
+        assert not mi.is_complete
+        grid = mpb.Grid(mi)
+        assert np.array_equal(grid.generating_points, gp)
+        with pytest.raises(ValueError):
+            grid.tree                                    # dds needs a complete set
+        for key, ref_key in (("coeffs1", "l2n1_ref"), ("coeffs3", "l2n3_ref")):
+            lag = mpb.LagrangePolynomial(mi, nxt[f"inc/{i}/{key}"], grid=grid)
+            trafo = mpb.LagrangeToNewton(lag)
+            op = trafo.transformation_operator
+            assert isinstance(op, MatrixOperator)
+            assert rel_err(op.array_repr_full, nxt[f"inc/{i}/operator_ref"]) <= 1e-10
+            newt = trafo()
+            ref = nxt[f"inc/{i}/{ref_key}"]
+            assert newt.coeffs.shape == ref.shape and rel_err(newt.coeffs, ref) <= 1e-10
+            back = mpb.NewtonToLagrange(newt)()
+            assert rel_err(back.coeffs, lag.coeffs) <= 1e-11
+    # operator algebra: (L2N) @ (N2L) is the identity operator
+    n2l = mpb.NewtonToLagrange(newt).transformation_operator
+    prod = op @ n2l
+    assert isinstance(prod, MatrixOperator)
+    assert np.max(np.abs(prod.array_repr_full - np.eye(len(mi)))) <= 1e-11
+    with pytest.raises(ValueError):
+        op @ np.ones(len(mi) + 1)
+
+
+def test_matrix_operator_on_device_tensors(mpb, nxt):
+    import torch
+    from minterpy_b200.polynomials import MatrixOperator
+    rng = np.random.default_rng(12)
+    T = rng.uniform(-1, 1, (301, 301))
+    c = rng.uniform(-1, 1, (301, 5))
+    op = MatrixOperator(torch.as_tensor(T, device="cuda"))
+    out = op @ torch.as_tensor(c, device="cuda")
+    assert out.is_cuda and rel_err(out.cpu().numpy(), T @ c) <= 1e-13
+    assert rel_err(op @ c[:, 0], T @ c[:, 0]) <= 1e-13              # NumPy in, NumPy out, 1-D
+    assert np.array_equal(op.array_repr_full, T)
