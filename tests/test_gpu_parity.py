@@ -498,3 +498,47 @@ print("OK", n)
                          text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
     assert out.stdout.strip().startswith("OK 76")
+
+
+def test_one_thread_per_gpu(mpb, golden_cfg):
+    """one process per GPU or one THREAD per GPU must both work.  Needs two
+    devices (skipped on a single-GPU box): a plan per device, threads that never call
+    cudaSetDevice themselves, inputs as NumPy (the library selects the plan's device) and as
+    tensors that live on the plan's device."""
+    import threading
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    g = golden_cfg("cfg2")
+    e, gp = g["exponents"], g["generating_points"]
+    rng = np.random.default_rng(5)
+    xx = rng.uniform(-1, 1, (20000, 4))
+    c = rng.uniform(-1, 1, (e.shape[0], 2))
+    v = rng.uniform(-1, 1, (e.shape[0], 3))
+    ref_plan = mpb.get_plan(e, gp, device=0)
+    want = (ref_plan.eval(xx, c), ref_plan.dds(v))
+    results, errors = {}, []
+
+    def work(dev):
+        try:
+            plan = mpb.get_plan(e, gp, device=dev)
+            assert plan.device == dev
+            for _ in range(3):
+                a = plan.eval(xx, c)
+                b = plan.dds(v)
+                xt = torch.as_tensor(xx, device=f"cuda:{dev}")
+                ct = torch.as_tensor(c, device=f"cuda:{dev}")
+                t = plan.eval(xt, ct)
+                assert t.device.index == dev
+                results[dev] = (a, b, t.cpu().numpy())
+        except Exception as ex:       # noqa: BLE001
+            errors.append((dev, ex))
+
+    threads = [threading.Thread(target=work, args=(d,)) for d in range(torch.cuda.device_count())]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    for dev, (a, b, t) in results.items():
+        assert np.array_equal(a, want[0]) and np.array_equal(b, want[1]) and np.array_equal(t, want[0])
