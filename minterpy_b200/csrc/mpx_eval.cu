@@ -177,6 +177,9 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
     const int me1 = (m >= 2) ? p.max_exp[1] : 0;
     double *ups = T1s + (size_t)(me1 + 1) * R * NT;   // [2][U-1][R][NT]: running product, sum
     const size_t up_stride = (size_t)(U > 1 ? U - 1 : 0) * R * NT;   // dimensions 3.. only
+    // coordinates of dimensions 2.. of this thread's points, [U][R][NT]: the folds read them
+    // with one address computation instead of rebuilding R global pointers per record
+    double *xs = ups + 2 * up_stride + tid;
 
     const int q = blockIdx.y;                                   // polynomial
     const double *coef_img = p.coef + (size_t)q * p.n_chunks * MPX_COEF_CAP;
@@ -213,13 +216,11 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
     double T0[R][L0P];
     double acc1[R];
     double t2[R], a2[R];          // running product and partial sum of dimension 2
-    const double *xrow[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         int64_t pt = tile0 + (int64_t)r * NT + tid;
         if (pt >= p.P) pt = p.P - 1;               // tail threads recompute the last point
         const double *xp = p.xx + pt * p.ld_xx;
-        xrow[r] = xp;
         const double x0 = xp[0];
         const int me0 = p.max_exp[0];
         T0[r][0] = 1.0;
@@ -239,6 +240,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
 #pragma unroll 1
         for (int u = 0; u < U; ++u) {
             const double xu = xp[2 + u];
+            xs[(size_t)(u * R + r) * NT] = xu;
             double t = 1.0;
 #pragma unroll 1
             for (int j = 0; j < p.start_exp[2 + u]; ++j) t *= xu - gps[(2 + u) * p.gp_rows + j];
@@ -293,11 +295,11 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
             const int e1 = w & 255;
             const int nf = (w >> 8) & 15;
             // a fold follows this record: fetch the coordinate of the level that will advance
-            // now (L1/L2 hit), so the load is hidden behind the record's FMAs
+            // now, so the load is hidden behind the record's FMAs
             double xadv[R];
             if (nf) {
 #pragma unroll
-                for (int r = 0; r < R; ++r) xadv[r] = __ldg(xrow[r] + 1 + nf);
+                for (int r = 0; r < R; ++r) xadv[r] = xs[(size_t)((nf - 1) * R + r) * NT];
             }
             uint32_t t1a = t1_base + (uint32_t)e1 * T1L::ROW_BYTES;
             LengthChain<L0P, R, A, NT, L0P / 2>::go(acc1, T0, cp, t1a, counts);
@@ -343,7 +345,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                             a2[r] = 0.0;
                             double tn = 1.0;
                             if (st) {
-                                const double xu = xrow[r][2];
+                                const double xu = xs[(size_t)r * NT];
 #pragma unroll 1
                                 for (int j = 0; j < st; ++j) tn *= xu - gps[2 * p.gp_rows + j];
                             }
@@ -365,7 +367,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                             low[r] = fma(tv[r], low[r], av[r]);
                             double tn = 1.0;
                             if (st) {
-                                const double xu = xrow[r][2 + u];
+                                const double xu = xs[(size_t)(u * R + r) * NT];
 #pragma unroll 1
                                 for (int j = 0; j < st; ++j) tn *= xu - gps[(2 + u) * p.gp_rows + j];
                             }
@@ -438,7 +440,7 @@ size_t eval_smem_bytes(const mpx_plan *pl, int R, int NT, int stages)
     const int U = m > 2 ? m - 2 : 0;
     const int me1 = m >= 2 ? pl->max_exp[1] : 0;
     size_t doubles = (size_t)((m * pl->gp_rows + 1) & ~1) + (size_t)(me1 + 1) * R * NT +
-                     (size_t)2 * (U > 1 ? U - 1 : 0) * R * NT;
+                     (size_t)2 * (U > 1 ? U - 1 : 0) * R * NT + (size_t)U * R * NT;
     return 128 + (size_t)stages * STAGE_BYTES + doubles * 8;
 }
 
