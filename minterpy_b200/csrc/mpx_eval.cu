@@ -210,6 +210,9 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
     } else {
         next_load = p.n_chunks;      // only thread 0 ever refills
     }
+    // "thread 0 still has chunks to request": one predicate for the polls in the record loop
+    // instead of a parameter load and a compare per record
+    bool refilling = next_load < p.n_chunks;
 
     // ---- per-point tables -------------------------------------------------------------
     const int64_t tile0 = (int64_t)blockIdx.x * (R * NT);
@@ -262,7 +265,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
     for (int c = 0; c < p.n_chunks; ++c) {
         const int s = c % S;
         const uint32_t ph = (uint32_t)(c / S) & 1u;
-        if (next_load < p.n_chunks) {
+        if (refilling) {
             // thread 0: refill every stage that all threads have released; if chunk c itself
             // has not been requested yet (its stage was busy at every earlier poll), wait.
             for (;;) {
@@ -271,7 +274,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                 if (next_load <= c) mbar_wait(&empty[sp], php);
                 else if (!mbar_test(&empty[sp], php)) break;
                 issue_load(next_load);
-                if (++next_load >= p.n_chunks) break;
+                if (++next_load >= p.n_chunks) { refilling = false; break; }
             }
         }
         mbar_wait(&full[s], ph);
@@ -279,12 +282,12 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
         uint32_t cp = smem_u32(ring + s * STAGE_BYTES + MPX_DESC_WORDS * 4);
         const int iend = MPX_DESC_HDR + (int)dw[0];
         for (int i = MPX_DESC_HDR; i < iend;) {
-            if (next_load < p.n_chunks) {
+            if (refilling) {
                 // thread 0, between records: hand a released stage straight back to the TMA
                 const int sp = next_load % S;
                 if (mbar_test(&empty[sp], (uint32_t)(next_load / S - 1) & 1u)) {
                     issue_load(next_load);
-                    ++next_load;
+                    refilling = ++next_load < p.n_chunks;
                 }
             }
             const uint32_t w = dw[i];
