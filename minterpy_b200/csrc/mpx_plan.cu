@@ -523,10 +523,12 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
         compile_tile_program(e, N, m, pl->tprog);
         // Worth it only for long dimension-0 tables (more than 5 k-steps, n > 19) whose tiles
         // carry almost no zero padding -- in practice full tensor grids (lp = inf).  Measured
-        // on the B200: cfg5 (6 % more FMAs than the DFMA tree kernel) 1.17e13 vs 8.8e12 pm/s;
-        // m=3, n=24, lp=2 (21 % more) 5.5e12 vs 7.3e12; cfg2 (27 % more, short tiles) 6.8e12 vs
-        // 8.6e12.  MPX_FORCE_TMMA=1 takes it whenever it was built (tests, experiments).
-        const int64_t tree_fma = pl->tree_ok ? pl->prog.fma_per_point : 0;
+        // on the B200: cfg5 (9 % more FMAs than the DFMA tree kernel) 1.18e13 vs 9.9e12 pm/s;
+        // m=3, n=24, lp=2 (about 25 % more) 5.5e12 vs 9.6e12; cfg2 (about 40 % more, short
+        // tiles) 6.8e12 vs 9.3e12.  MPX_FORCE_TMMA=1 takes it whenever it was built (tests,
+        // experiments).
+        // (the threshold was tuned on FMA counts that included one more per leaf)
+        const int64_t tree_fma = pl->tree_ok ? pl->prog.fma_per_point + pl->prog.n_leaves : 0;
         pl->tprog.usable = getenv("MPX_FORCE_TMMA") != nullptr || !pl->tree_ok ||
                            (pl->tprog.ks_max > 5 && 100 * pl->tprog.fma_per_point <= 110 * tree_fma);
     }
