@@ -300,13 +300,26 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
             // a fold follows this record: fetch the coordinate of the level that will advance
             // now, so the load is hidden behind the record's FMAs
             double xadv[R];
+            // the common fold -- dimension 2 takes the record's sum and advances by one, nothing
+            // irregular, not the end of the program -- gets a short path of its own; what it
+            // needs is fetched here, behind the record's FMAs
+            const bool simple_fold = (w & (0xF00u | MPX_D_IRREG | MPX_D_LAST)) == 0x100u;
+            double g2s = 0.0;
             if (nf) {
 #pragma unroll
                 for (int r = 0; r < R; ++r) xadv[r] = xs[(size_t)((nf - 1) * R + r) * NT];
+                if (simple_fold) g2s = gps[2 * p.gp_rows + (int)((w >> 14) & 255u)];
             }
             uint32_t t1a = t1_base + (uint32_t)e1 * T1L::ROW_BYTES;
             LengthChain<L0P, R, A, NT, L0P / 2>::go(acc1, T0, cp, t1a, counts);
-            if (nf) {
+            if (simple_fold) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    a2[r] = fma(t2[r], acc1[r], a2[r]);
+                    t2[r] *= xadv[r] - g2s;
+                    acc1[r] = 0.0;
+                }
+            } else if (nf) {
                 // fold finished subtrees upwards: levels 0..nf-1 (dimensions 2..nf+1)
                 int adv = 1, cur = (w >> 14) & 255;
                 const bool irregular = (w & MPX_D_IRREG) != 0;

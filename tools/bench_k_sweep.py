@@ -1,0 +1,16 @@
+import sys, os, json, numpy as np, torch
+sys.path.insert(0,'/root/repo'); sys.path.insert(0,'/root/repo/tests/golden')
+import golden_io, minterpy_b200 as mpb
+tag=sys.argv[1]; P=int(sys.argv[2])
+g=golden_io.load(tag); e,gp=g['exponents'],g['generating_points']
+plan=mpb.get_plan(e,gp)
+xx=torch.rand((P,e.shape[1]),dtype=torch.float64,device='cuda')*2-1
+for k in (4,6,8,12,16,24,32,48):
+    c=torch.rand((e.shape[0],k),dtype=torch.float64,device='cuda')
+    out=torch.empty((P,k),dtype=torch.float64,device='cuda')
+    for _ in range(2): plan._eval_torch(xx,c,out=out)
+    ts=[]
+    for _ in range(3):
+        a,b=torch.cuda.Event(enable_timing=True),torch.cuda.Event(enable_timing=True)
+        a.record(); plan._eval_torch(xx,c,out=out); b.record(); torch.cuda.synchronize(); ts.append(a.elapsed_time(b))
+    print(tag,'mink',os.environ.get('MPX_EVAL_MMA_MIN_K','8'),'k',k,'%.2f ms'%np.median(ts))
