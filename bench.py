@@ -328,7 +328,9 @@ def main():
         other = plan.info(_lib.INFO_EVAL_OTHER_FP64)
         model = model_flops_per_point(e, k)
         peak_dfma, peak_dmma = measured_fp64_peak()
-        tensor_path = k >= 8 and m <= 8          # mpx_eval_mma.cu (DMMA), else the tree kernel
+        mma_min_k = plan.info(_lib.INFO_MMA_MIN_K)     # 0: never; else the smallest k on DMMA
+        many_poly = mma_min_k > 0 and k >= mma_min_k
+        tensor_path = many_poly                 # mpx_eval_mma.cu (DMMA), else the tree kernel
         if tensor_path:
             # per point: every monomial (padded to 32) is formed with m-1 DMUL and contracted
             # against k (padded to the CTA tile) coefficients on the tensor cores
@@ -370,7 +372,7 @@ def main():
                     "measured_dmma_peak": peak_dmma,
                     "flops_per_point_model": model, "flops_per_point_executed": executed,
                     "fma_per_point": fma,
-                    "kernel": ("eval_mma_kernel" if (k >= 8 and m <= 8) else
+                    "kernel": ("eval_mma_kernel" if many_poly else
                                "eval_tmma_kernel" if tensor_path else "eval_tree_kernel"),
                     "kernel_ms": kernel_ms,
                     "hbm_gbs": P * 8 * (m + k) / (kernel_ms * 1e-3) / 1e9}

@@ -72,10 +72,12 @@ enum {
     MPX_INFO_SCRATCH_BYTES = 7,/* device scratch currently held by the plan                  */
     MPX_INFO_EVAL_OTHER_FP64 = 8, /* FP64 adds/multiplies besides the FMAs, per point        */
     MPX_INFO_CHUNKS = 9,       /* chunks of the evaluation program                           */
-    MPX_INFO_SMALLK_KERNEL = 10, /* kernel used for k < 8: 0 = DFMA tree, 1 = tensor-core tree,
+    MPX_INFO_SMALLK_KERNEL = 10, /* kernel for k below MPX_INFO_MMA_MIN_K: 0 = DFMA tree, 1 = tensor-core tree,
                                   2 = shared-memory-table tensor kernel (long dimension 0)   */
-    MPX_INFO_TMMA_FMA = 11     /* FMAs per point and polynomial of the tensor-core tree kernel
+    MPX_INFO_TMMA_FMA = 11,    /* FMAs per point and polynomial of the tensor-core tree kernel
                                   (tile padding included), 0 if it was not built             */
+    MPX_INFO_MMA_MIN_K = 12    /* smallest k evaluated by the many-polynomial tensor kernel
+                                  (4, 8 or 13, by leaf length; 1: every k; 0: never, m > 8)     */
 };
 int mpx_plan_info(const mpx_plan *plan, int what, int64_t *value_out);
 
@@ -103,8 +105,9 @@ int mpx_eval(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
  * (held by every GPU that loads the library, until exit) instead of plan scratch that may
  * have to grow; the call allocates and frees nothing.
  *   - limit: the packed coefficients of one call must fit 8 MiB.  They take
- *     chunks * 512 * k * 8 bytes for k < 8 (chunks = MPX_INFO_CHUNKS) and about 1.1 * N * k * 8
- *     bytes (k rounded up to 8, 16, 32 or a multiple of 64) for k >= 8: up to 32 polynomials per
+ *     chunks * 1024 * k * 8 bytes for k below MPX_INFO_MMA_MIN_K (chunks = MPX_INFO_CHUNKS) and
+ *     about 1.1 * N * k * 8 bytes (k rounded up to 8, 16, 32 or a multiple of 64) from there on:
+ *     up to 32 polynomials per
  *     call at BASELINE config 2.  Beyond that the call returns MPX_ERR_UNSUPPORTED and does
  *     nothing -- split k, or use mpx_eval.
  *   - the first call on a device looks the array's address up (set-up); make that first call

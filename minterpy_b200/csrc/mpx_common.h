@@ -195,6 +195,7 @@ int mpx_launch_dds(mpx_plan *plan, double *vals, int k, int64_t ld, cudaStream_t
 int mpx_ensure_scratch(mpx_plan *plan, size_t bytes);
 // tensor-core (many polynomials) evaluation path, mpx_eval_mma.cu
 bool mpx_mma_eligible(const mpx_plan *plan, int k);
+int mpx_mma_min_k(const mpx_plan *plan);      // smallest k that prefers this kernel to the tree kernel
 size_t mpx_mma_scratch_bytes(const mpx_plan *plan, int k);
 // orders_h (m entries, host) != nullptr: evaluate the partial derivative of those orders
 int mpx_launch_eval_mma(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,

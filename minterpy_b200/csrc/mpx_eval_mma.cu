@@ -281,12 +281,26 @@ size_t mma_smem_bytes(const mpx_plan *pl, int nt8, int nw)
 }  // namespace
 
 
+// Smallest k that goes to this kernel when the tree kernel could take the plan as well.
+// Crossover against the tree kernel run once per polynomial (measured, 1e6 points): index sets
+// with long leaves (cfg2: 10 monomials per leaf, cfg4: 7) are faster on the tree kernel up to
+// k = 12 (cfg2 k = 8: 21 vs 32 ms, k = 12: 32 vs 43 ms; level at k = 16); sets with short leaves
+// (cfg3: 2.7) are record-bound there: k = 8 takes 26 vs 65 ms, and even k = 4, padded to the
+// 8-column tile here, 26 vs 33 ms.
+int mpx_mma_min_k(const mpx_plan *pl)
+{
+    static const int env_min_k = getenv("MPX_EVAL_MMA_MIN_K") ? atoi(getenv("MPX_EVAL_MMA_MIN_K")) : 0;
+    if (env_min_k > 0) return env_min_k;
+    if (pl->tree_ok && pl->prog.n_leaves > 0 && pl->N >= 6 * pl->prog.n_leaves) return 13;
+    if (pl->tree_ok && pl->prog.n_leaves > 0 && pl->N < 4 * pl->prog.n_leaves) return 4;
+    return 8;
+}
+
 bool mpx_mma_eligible(const mpx_plan *pl, int k)
 {
-    static const int min_k = getenv("MPX_EVAL_MMA_MIN_K") ? atoi(getenv("MPX_EVAL_MMA_MIN_K")) : 8;
     // the product tables of at least 64 points must fit shared memory, else the tree kernel
     // runs; plans the tree kernel cannot take (dimension-0 exponent > 64) come here for every k
-    return (k >= min_k || !pl->tree_ok) && pl->m <= 8 && pl->d_exp64 != nullptr &&
+    return (k >= mpx_mma_min_k(pl) || !pl->tree_ok) && pl->m <= 8 && pl->d_exp64 != nullptr &&
            mma_smem_bytes(pl, mma_nt8_for(k), 2) <= MMA_SMEM_LIMIT;
 }
 

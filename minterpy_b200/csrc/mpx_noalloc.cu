@@ -8,8 +8,9 @@
 // library's device image instead, so the call itself allocates nothing.
 //
 // Cost and limits: every GPU that loads libminterpy_b200.so holds MPX_NOALLOC_BYTES (8 MiB)
-// for the array until the process exits.  A call with k < 8 polynomials needs chunks * 512 * k
-// doubles (chunks = MPX_INFO_CHUNKS of the plan), one with more about 1.06 * N * k doubles; it
+// for the array until the process exits.  A call with few polynomials (k below the plan's
+// MPX_INFO_MMA_MIN_K) needs chunks * 1024 * k doubles (chunks = MPX_INFO_CHUNKS of the plan), one
+// with more about 1.06 * N * k doubles; it
 // is refused with MPX_ERR_UNSUPPORTED if that exceeds the array.  All plans and all calls on a device share the one array: it still holds the previous
 // call's image when the next call starts (every slot the next call reads is rewritten first,
 // padding included, so nothing has to be cleared), and two calls whose kernels overlap on the

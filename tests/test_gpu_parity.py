@@ -283,7 +283,8 @@ def test_dense_apply(mpb):
 
 @pytest.mark.parametrize("k", [8, 9, 16, 31, 64, 100])
 def test_many_polynomials_tensor_core_path(mpb, golden_cfg, k):
-    """k >= 8 takes the DMMA kernel (csrc/mpx_eval_mma.cu); same tolerance as the tree kernel."""
+    """Many polynomials: the DMMA kernel (csrc/mpx_eval_mma.cu) from k = 8 (short leaves, cfg3)
+    or k = 13 (long leaves, cfg2), the tree kernel below that; one tolerance for both."""
     for tag, npts in (("cfg3", 333), ("cfg2", 97)):
         g = golden_cfg(tag)
         e, gp = g["exponents"], g["generating_points"]
