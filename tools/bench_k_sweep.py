@@ -1,3 +1,8 @@
+#!/usr/bin/env python
+"""Evaluation time against the number of polynomials k (device-resident inputs, CUDA events,
+median of 3 after 2 warm-ups): where the tree kernel run once per polynomial and the
+many-polynomial tensor kernel cross.  usage: bench_k_sweep.py <cfgN> <points>;
+MPX_EVAL_MMA_MIN_K=9999 forces the tree kernel, =1 the tensor kernel."""
 import sys, os, json, numpy as np, torch
 sys.path.insert(0,'/root/repo'); sys.path.insert(0,'/root/repo/tests/golden')
 import golden_io, minterpy_b200 as mpb
