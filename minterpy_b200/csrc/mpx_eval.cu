@@ -515,6 +515,21 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
     if (stages > MPX_STAGES) stages = MPX_STAGES;
     if (stages < 2) stages = 2;
     const Variant *v = nullptr;
+    // Index sets with long leaves (>= 8 monomials per leaf: cfg2, cfg5) run 1-2 % faster as two
+    // independent CTAs of 128 threads per SM, each with a two-stage ring, than as one CTA of
+    // 256: the CTAs drift apart and fill each other's gaps at leaf and record boundaries.
+    // Short-leaf sets lose as much (more records per chunk, the shallow ring runs dry).
+    static const bool no_pair = getenv("MPX_EVAL_NO_CTA_PAIR") != nullptr;
+    if (env_stages == 0 && !no_pair && pl->prog.n_leaves > 0 && pl->N >= 8 * pl->prog.n_leaves) {
+        int sm_total = 0;
+        MPX_CUDA(cudaDeviceGetAttribute(&sm_total, cudaDevAttrMaxSharedMemoryPerMultiprocessor, pl->device));
+        for (int i = 0; i < n_standard && !v; ++i)
+            if (variants[i].l0p == l0p && variants[i].nt == 128 && variants[i].r > 1 &&
+                2 * (eval_smem_bytes(pl, variants[i].r, 128, 2) + 1024) <= (size_t)sm_total) {
+                v = &variants[i];
+                stages = 2;
+            }
+    }
     for (int i = 0; i < n_standard && !v; ++i)
         if (variants[i].l0p == l0p &&
             eval_smem_bytes(pl, variants[i].r, variants[i].nt, stages) <= (size_t)smem_max)
