@@ -543,3 +543,22 @@ def test_one_thread_per_gpu(mpb, golden_cfg):
     assert not errors, errors
     for dev, (a, b, t) in results.items():
         assert np.array_equal(a, want[0]) and np.array_equal(b, want[1]) and np.array_equal(t, want[0])
+
+
+def test_kernel_choice_by_leaf_length(mpb, golden_cfg):
+    """MPX_INFO_MMA_MIN_K: long-leaf sets (cfg2, cfg4, cfg5) keep the tree kernel up to k = 12,
+    short-leaf sets (cfg3) go to the many-polynomial tensor kernel from k = 4; values on both
+    sides of each threshold agree with the oracle to the one tolerance."""
+    from minterpy_b200 import _lib
+    want = {"cfg2": 13, "cfg4": 13, "cfg5": 13, "cfg3": 4}
+    rng = np.random.default_rng(31)
+    for tag, min_k in want.items():
+        g = golden_cfg(tag)
+        e, gp = g["exponents"], g["generating_points"]
+        plan = mpb.get_plan(e, gp)
+        assert plan.info(_lib.INFO_MMA_MIN_K) == min_k
+        xx = rng.uniform(-1, 1, (70, e.shape[1]))
+        for k in (min_k - 1, min_k):
+            c = rng.uniform(-1, 1, (e.shape[0], k))
+            ref = oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=4)
+            assert rel_err(plan.eval(xx, c), ref) <= EVAL_RTOL, (tag, k)
