@@ -57,7 +57,7 @@ def _lin(xp_is_torch):
     return np.linalg
 
 
-def _diag_weights(weights, like):
+def _diag_weights(weights):
     if weights is None:
         return None
     if weights.ndim == 1:
@@ -71,7 +71,7 @@ def _diag_weights(weights, like):
 def solve_least_squares(rr, yy, weights=None, lstsq_solver="lstsq", **kwargs):
     """``ordinary_regression.py:278-353``; solvers ``lstsq``, ``inv``, ``pinv``, ``qr``, or a
     callable ``solver(rr, yy, weights, **kwargs)``."""
-    ww = _diag_weights(weights, rr)
+    ww = _diag_weights(weights)
     if callable(lstsq_solver):
         return lstsq_solver(rr, yy, ww, **kwargs)
     name = lstsq_solver.lower()
@@ -128,7 +128,7 @@ def compute_loocv_error(rr, coeffs, yy, weights=None):
     var = yy.var(unbiased=False) if on_device else np.var(yy)
     if rr.shape[0] < rr.shape[1]:
         return float("inf"), float("inf")
-    ww = _diag_weights(weights, rr)
+    ww = _diag_weights(weights)
     if ww is None:
         gram_inv = la.pinv(rr.T @ rr)
         hi = ((rr @ gram_inv) * rr).sum(1)          # diag(R G^+ R^T) without the P x P matrix

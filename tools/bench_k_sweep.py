@@ -3,9 +3,18 @@
 median of 3 after 2 warm-ups): where the tree kernel run once per polynomial and the
 many-polynomial tensor kernel cross.  usage: bench_k_sweep.py <cfgN> <points>;
 MPX_EVAL_MMA_MIN_K=9999 forces the tree kernel, =1 the tensor kernel."""
-import sys, os, json, numpy as np, torch
-sys.path.insert(0,'/root/repo'); sys.path.insert(0,'/root/repo/tests/golden')
-import golden_io, minterpy_b200 as mpb
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+import golden_io  # noqa: E402
+import minterpy_b200 as mpb  # noqa: E402
+
 tag=sys.argv[1]; P=int(sys.argv[2])
 g=golden_io.load(tag); e,gp=g['exponents'],g['generating_points']
 plan=mpb.get_plan(e,gp)
