@@ -153,36 +153,164 @@ def cpu_baseline(e, gp, k, target_seconds=12.0, seed=1):
             "seconds": dt, "points": P}
 
 
+# ---- the unmodified reference on the host cores -------------------------------------------
+# baseline/_ref holds the pip-installed reference (tools/make_baseline_ref.py; git-ignored, it
+# travels to the GPU box).  What is timed is its own public callable,
+# minterpy.utils.eval_newton_polynomials(xx, c, e, gp, batch_size=B)  (utils.py:247-343), as-is
+# in one process, and process-parallel over point shards on all host cores.
+_REF = {}
+
+
+def _ref_eval(lo, hi):
+    g = _REF
+    return g["fn"](g["xx"][lo:hi], g["c"], g["e"], g["gp"], batch_size=g["batch"])
+
+
+def _ref_worker(span):
+    from threadpoolctl import threadpool_limits
+    with threadpool_limits(1):             # one BLAS thread per worker process
+        return float(_ref_eval(*span).sum())
+
+
+def reference_available():
+    from ref_shim import reference_location
+    return reference_location() is not None
+
+
+def reference_cpu_baseline(e, gp, k, target_seconds=12.0, seed=1, cores=None):
+    """The reference itself on a bounded sample: `value` = process-parallel over all host
+    cores, `single_core_value` = the call as-is in one process.  JIT warm-up excluded."""
+    import multiprocessing as mp_
+    from ref_shim import load_reference
+    ref = load_reference()
+    fn = ref.utils.eval_newton_polynomials
+    cores = cores or os.cpu_count() or 1
+    N, m = e.shape
+    rng = np.random.default_rng(seed)
+    c = rng.uniform(-1, 1, (N, k))
+    c = c[:, 0] if k == 1 else c
+    batch = max(64, int((128 << 20) // (8 * N)))      # batch * N * 8 B <= 128 MB per process
+    _REF.update(fn=fn, c=c, e=e, gp=gp, batch=batch, xx=rng.uniform(-1, 1, (64, m)))
+    _ref_eval(0, 64)                                                   # JIT compile
+    probe = 2048
+    _REF["xx"] = rng.uniform(-1, 1, (probe, m))
+    t = time.perf_counter()
+    _ref_eval(0, probe)
+    rate1 = probe / max(time.perf_counter() - t, 1e-6)                 # points/s, one process
+    P1 = int(max(probe, rate1 * 3.0))
+    P = int(max(cores * 256, min(rate1 * cores * target_seconds * 0.8, 20_000_000)))
+    _REF["xx"] = xx = rng.uniform(-1, 1, (max(P, P1), m))
+    t = time.perf_counter()
+    _ref_eval(0, P1)
+    dt1 = time.perf_counter() - t
+    # shards: 4 per core so that the tail is short; children are forked (they inherit the
+    # arrays and the compiled kernels; nothing in this process has touched CUDA)
+    nshard = cores * 4
+    bounds = np.linspace(0, P, nshard + 1).astype(np.int64)
+    spans = [(int(a), int(b)) for a, b in zip(bounds[:-1], bounds[1:]) if b > a]
+    with mp_.get_context("fork").Pool(cores) as pool:
+        pool.map(_ref_worker, [(0, 64)] * cores)                       # start-up, untimed
+        t = time.perf_counter()
+        pool.map(_ref_worker, spans, chunksize=1)
+        dt = time.perf_counter() - t
+    del xx
+    return {"value": P * N / dt, "unit": "point*monomials/s", "cores": cores, "kind": "reference",
+            "sample": f"{P} points of the workload ({dt:.1f} s): minterpy.utils."
+                      f"eval_newton_polynomials (unmodified, baseline/_ref), batch_size={batch}, "
+                      f"point shards over {cores} forked processes",
+            "single_core_value": P1 * N / dt1,
+            "single_core_sample": f"{P1} points, the call as-is in one process ({dt1:.1f} s)",
+            "seconds": dt, "points": P}
+
+
 def run_reference(args):
-    """`--impl reference`: the CPU path only (rank 0; other ranks exit)."""
+    """`--impl reference`: the CPU path only (rank 0; other ranks exit).  The unmodified
+    reference where baseline/_ref imports, else the oracle port (the import error is kept in
+    the line)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     e, gp = load_workload(args.workload)
     desc, _, k = WORKLOADS[args.workload]
     N = e.shape[0]
-    per_step = max(4.0, min(30.0, 150.0 / max(args.steps + args.warmup, 1)))
+    per_step = args.cpu_seconds or max(4.0, min(30.0, 150.0 / max(args.steps + args.warmup, 1)))
+    runner, why_port = cpu_baseline, None
+    if args.cpu_kind != "port":
+        try:
+            if not reference_available():
+                raise ImportError("baseline/_ref is absent (tools/make_baseline_ref.py)")
+            reference_cpu_baseline(e, gp, k, target_seconds=0.5)
+            runner = reference_cpu_baseline
+        except Exception as exc:       # noqa: BLE001 -- any import/JIT failure: fall back to the port
+            why_port = f"{type(exc).__name__}: {exc}"
     for _ in range(args.warmup):
-        cpu_baseline(e, gp, k, target_seconds=1.0)
-    vals, pts, secs = [], 0, 0.0
+        runner(e, gp, k, target_seconds=1.0)
+    pts, secs, last = 0, 0.0, None
     for s in range(args.steps):
-        b = cpu_baseline(e, gp, k, target_seconds=per_step, seed=100 + s)
-        vals.append(b["value"])
-        pts += b["points"]
-        secs += b["seconds"]
+        last = runner(e, gp, k, target_seconds=per_step, seed=100 + s)
+        pts += last["points"]
+        secs += last["seconds"]
     value = pts * N / secs
-    import oracle
+    base = {"value": value, "unit": "point*monomials/s", "cores": last["cores"],
+            "kind": last["kind"], "sample": f"{pts} points over {args.steps} steps; " + last["sample"],
+            "single_core_value": last["single_core_value"]}
+    if why_port:
+        base["reference_unavailable"] = why_port
+    if last["kind"] == "reference" and not args.no_port:
+        port = cpu_baseline(e, gp, k, target_seconds=min(per_step, 6.0))
+        base["port_value"] = port["value"]
+        base["port_single_core_value"] = port["single_core_value"]
     line = {"impl": "reference", "metric": "newton_evals_per_sec", "value": value,
             "unit": "point*monomials/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(args.steps, 1),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": {"workload": f"{args.workload}: {desc}",
-                                            "monomials": int(N), "k": k},
-            "cpu_baseline": {"value": value, "unit": "point*monomials/s",
-                             "cores": oracle.num_threads(), "kind": "port",
-                             "sample": f"{pts} points over {args.steps} steps"},
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": workload_config(args, N, k, desc, e.shape[1], args.gpus),
+            "cpu_baseline": base,
             "e2e": {"value": value, "unit": "point*monomials/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def job_points(args, world):
+    """(points of this job per GPU -- the largest shard --, points of the whole job)."""
+    _, P, _ = WORKLOADS[args.workload]
+    if args.scaling == "strong":
+        if args.workload == "cfg5":
+            P = 1_000_000_000                # BASELINE config 5 as written: 1e9 points in all
+        if args.points:
+            P = args.points
+        return P - (world - 1) * (P // world), P
+    if args.points:
+        P = args.points
+    return P, world * P
+
+
+def workload_config(args, N, k, desc, m, world):
+    """The `config` object, identical in both arms (the driver compares them)."""
+    per_gpu, total = job_points(args, world)
+    return {"workload": f"{args.workload}: {desc}", "monomials": int(N), "k": k,
+            "points_per_gpu": int(per_gpu), "points_total": int(total),
+            "parallelism": f"points sharded x{world}",
+            "l2": ("inputs (points) larger than L2, streamed once per step"
+                   if per_gpu * 8 * (m + k) >= (256 << 20) else
+                   "256 MB buffer written between timed steps (inputs fit L2); "
+                   "timed region = sum of per-step CUDA-event times")}
+
+
+def cpu_baseline_subprocess(workload, seconds=12.0):
+    """The CPU figure for the main line: `bench.py --impl reference` in a child process (it
+    forks worker processes, which this process -- CUDA initialised -- must not do)."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--workload", workload,
+           "--steps", "1", "--warmup", "0", "--cpu-seconds", str(seconds)]
+    env = {k: v for k, v in os.environ.items()
+           if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE")}
+    try:
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env).stdout
+        for line in reversed(out.splitlines()):
+            if line.startswith("{"):
+                return json.loads(line)["cpu_baseline"]
+    except (OSError, ValueError, KeyError, subprocess.TimeoutExpired):
+        pass
+    return None
 
 
 def main():
@@ -192,9 +320,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--points", type=int, default=None, help="points per GPU (default: workload's)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: the workload's points on EVERY GPU; strong: the workload's points "
+                         "(cfg5: 1e9) split over the GPUs, broadcast and gather inside e2e")
+    ap.add_argument("--points", type=int, default=None,
+                    help="points per GPU (weak) / of the whole job (strong); default: workload's")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=None, help="CPU sample size per step")
+    ap.add_argument("--cpu-kind", default="auto", choices=["auto", "port"])
+    ap.add_argument("--no-port", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -216,16 +351,19 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    desc, P, k = WORKLOADS[args.workload]
-    if args.points:
-        P = args.points
+    desc, _, k = WORKLOADS[args.workload]
+    strong = args.scaling == "strong"
+    P, P_job = job_points(args, world)
+    if strong:
+        a, b = mpd.shard_bounds(P_job, rank, world)
+        P = b - a                            # this rank's shard
     cfg = int(args.workload[3:])
     e, gp = load_workload(args.workload)
     N, m = e.shape
     plan = mpb.get_plan(e, gp, device=local)
 
     # synthetic inputs: points per rank from Philox on the device; coefficients drawn on rank 0
-    # and broadcast once over NCCL (the only collective; it is outside the timed region)
+    # and broadcast once over NCCL (weak: outside the timed region; strong: inside e2e)
     gen = torch.Generator(device=dev).manual_seed(20261106 + 1000 * cfg + rank)
     xx = torch.rand((P, m), generator=gen, dtype=torch.float64, device=dev) * 2 - 1
     coeffs = torch.from_numpy(golden_io.draw_uniform(7 + cfg, (N, k))).to(dev)
@@ -242,6 +380,13 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -270,45 +415,86 @@ def main():
     step_ms = [starts[i].elapsed_time(stops[i]) for i in range(args.steps)]
     # without a flush the steps run back to back: first start to last stop is the timed region
     total_ms = starts[0].elapsed_time(stops[-1]) if flush is None else float(sum(step_ms))
-    if world > 1:
-        t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = t.item()
+    total_ms = max_over_ranks(total_ms)
     ms_per_step = total_ms / args.steps
-    value = world * P * N / (ms_per_step * 1e-3)
+    value = P_job * N / (ms_per_step * 1e-3)
 
-    # ---- end to end through the public NumPy API, pinned host buffers --------------------
+    # ---- end to end through the public NumPy API, HOST buffers ---------------------------
+    # pinned: the caller's points are page-locked (torch pin_memory); pageable: an ordinary
+    # NumPy array (np.random), which the library stages through its own pinned ring.
+    # strong scaling: the step also holds the NCCL broadcast of the coefficients before and the
+    # all_gather of the result shards after the evaluation (one job: broadcast, shard, gather).
     e2e = None
+    e2e_pageable = None
     if not args.no_e2e:
-        Pe = P
-        xh = torch.empty((Pe, m), dtype=torch.float64, pin_memory=True)
-        xh.copy_(xx[:Pe])
-        xh_np = xh.numpy()
         ch = coeffs.cpu().numpy()
         ch1 = ch[:, 0] if k == 1 else ch
         e2e_steps = max(1, min(args.steps, 3))
-        for _ in range(2):                                      # warm-up (plan staging buffers,
-            y = mpb.eval_newton_polynomials(xh_np, ch1, e, gp)   # pinned result block)
-            del y
-        barrier()
-        e2e_ms = []
-        for _ in range(e2e_steps):
-            t = time.perf_counter()
-            y = mpb.eval_newton_polynomials(xh_np, ch1, e, gp)
-            e2e_ms.append((time.perf_counter() - t) * 1e3)
-            assert y.shape[0] == Pe
-            del y
-        barrier()
-        dt = float(np.mean(e2e_ms)) * 1e-3
-        if world > 1:
-            tt = torch.tensor([dt], dtype=torch.float64, device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            dt = tt.item()
-        e2e = {"value": world * Pe * N / dt, "unit": "point*monomials/s",
-               "h2d_bytes_per_step": int(Pe * m * 8 + N * k * 8), "d2h_bytes_per_step": int(Pe * k * 8),
-               "ms_per_step": dt * 1e3, "step_ms": e2e_ms,
-               "api": "minterpy_b200.eval_newton_polynomials(numpy)"}
+        def e2e_numpy(x_np):
+            times = []
+            for it in range(2 + e2e_steps):            # 2 warm-ups (staging buffers, pinned result)
+                barrier()
+                t = time.perf_counter()
+                y = mpb.eval_newton_polynomials(x_np, ch1, e, gp)
+                dt = time.perf_counter() - t
+                assert y.shape[0] == x_np.shape[0]
+                del y
+                if it >= 2:
+                    times.append(dt * 1e3)
+            dt = max_over_ranks(float(np.mean(times)) * 1e-3)
+            return {"value": P_job * N / dt, "unit": "point*monomials/s",
+                    "h2d_bytes_per_step": int(P * m * 8 + N * k * 8),
+                    "d2h_bytes_per_step": int(P * k * 8),
+                    "ms_per_step": dt * 1e3, "step_ms": times,
+                    "api": "minterpy_b200.eval_newton_polynomials(numpy)"}
+
+        def e2e_one_job(xh, yh):
+            """Strong scaling, N > 1: ONE job -- coefficients broadcast from rank 0 over NCCL,
+            every rank uploads and evaluates its shard of the points, the result shards are
+            all-gathered over NVLink, and every rank reads its shard back to the host."""
+            times = []
+            c1 = coeffs[:, 0] if k == 1 else coeffs
+            for it in range(2 + e2e_steps):
+                barrier()
+                t = time.perf_counter()
+                dist.broadcast(coeffs, src=0)
+                xx.copy_(xh, non_blocking=True)
+                y = mpb.eval_newton_polynomials(xx, c1, e, gp)
+                full = mpd.gather_values(y.reshape(P, k), P_job)
+                yh.copy_(y.reshape(P, k), non_blocking=True)
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t
+                assert full.shape[0] == P_job
+                del full, y
+                if it >= 2:
+                    times.append(dt * 1e3)
+            dt = max_over_ranks(float(np.mean(times)) * 1e-3)
+            return {"value": P_job * N / dt, "unit": "point*monomials/s",
+                    "h2d_bytes_per_step": int(P * m * 8), "d2h_bytes_per_step": int(P * k * 8),
+                    "ms_per_step": dt * 1e3, "step_ms": times,
+                    "api": "minterpy_b200.eval_newton_polynomials(torch) + distributed.gather_values",
+                    "includes": "NCCL broadcast of the coefficients, H2D of the point shard, "
+                                "evaluation, all_gather of the result shards, D2H of the shard"}
+
+        xh = torch.empty((P, m), dtype=torch.float64, pin_memory=True)
+        xh.copy_(xx)
+        if strong and world > 1:
+            yh = torch.empty((P, k), dtype=torch.float64, pin_memory=True)
+            e2e = e2e_one_job(xh, yh)
+            del yh
+        else:
+            e2e = e2e_numpy(xh.numpy())
+        e2e["host_memory"] = "page-locked input (torch pin_memory), page-locked result"
         del xh
+        if not (strong and world > 1):
+            xp = np.empty((P, m))                       # ordinary pageable memory, same points
+            blk = 1 << 22
+            for a in range(0, P, blk):
+                xp[a:a + blk] = xx[a:a + blk].cpu().numpy()
+            e2e_pageable = e2e_numpy(xp)
+            e2e_pageable["host_memory"] = ("pageable input (plain numpy array), result array "
+                                           "allocated by the API")
+            del xp
 
     gather_ms = None
     if world > 1:
@@ -319,8 +505,7 @@ def main():
         full = mpd.gather_values(out, world * P)
         g1.record()
         barrier()
-        gather_ms = g0.elapsed_time(g1)
-        assert full.shape[0] == world * P
+        gather_ms = max_over_ranks(g0.elapsed_time(g1))
         del full
 
     if rank == 0:
@@ -376,19 +561,15 @@ def main():
                                "eval_tmma_kernel" if tensor_path else "eval_tree_kernel"),
                     "kernel_ms": kernel_ms,
                     "hbm_gbs": P * 8 * (m + k) / (kernel_ms * 1e-3) / 1e9}
-        cpu = None if args.no_cpu else cpu_baseline(e, gp, k)
-        if cpu:
-            cpu.pop("seconds"), cpu.pop("points")
+        cpu = None if args.no_cpu else cpu_baseline_subprocess(args.workload, args.cpu_seconds or 12.0)
+        cfgd = workload_config(args, N, k, desc, m, world)
         line = {"metric": "newton_evals_per_sec", "value": value, "unit": "point*monomials/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling,
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"{args.workload}: {desc}", "monomials": int(N), "k": k,
-                           "points_per_gpu": int(P), "parallelism": f"points sharded x{world}",
-                           "l2": ("inputs (points) larger than L2, streamed once per step" if flush is None else
-                                  "256 MB buffer written between timed steps (inputs fit L2); "
-                                  "timed region = sum of per-step CUDA-event times")},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
+                "config": cfgd,
+                "clocks": clocks, "e2e": e2e, "e2e_pageable": e2e_pageable,
+                "gpu_launches": 2 * args.steps,
                 "roofline": roofline, "cpu_baseline": cpu, "gather_ms": gather_ms,
                 "step_ms": step_ms}
         print(json.dumps(line))

@@ -51,16 +51,36 @@ def install():
     for name in ("minterpy.core.utils", "minterpy.core.multi_index"):
         _set(mods[name], "is_lexicographically_complete", is_lexicographically_complete)
 
+    # The operators must BE reference operators (tests/test_transformation.py:81 of the reference
+    # checks isinstance(operator, OperatorABC)): derive installed variants from both the CUDA
+    # operator and OperatorABC; `op @ op` returns the reference's own MatrixOperator.
+    operator_abc = importlib.import_module("minterpy.core.ABC").OperatorABC
+    ref_matrix_operator = importlib.import_module("minterpy.schemes.matrix_operator").MatrixOperator
+
+    def _installed(base):
+        def __init__(self, transformation):
+            operator_abc.__init__(self, transformation, None)
+            base.__init__(self, transformation.grid, transformation)
+
+        def _make_matrix_operator(self, matrix):
+            return ref_matrix_operator(self.transformation, matrix)
+
+        return type(base.__name__, (base, operator_abc),
+                    {"__init__": __init__, "_make_matrix_operator": _make_matrix_operator,
+                     "__doc__": base.__doc__})
+
+    installed_dds, installed_node_eval = _installed(DDSOperator), _installed(NodeEvalOperator)
+
     def l2n_operator(transformation):
         grid = transformation.grid
         if grid.multi_index.is_complete and not transformation.origin_poly.indices_are_separate:
-            return DDSOperator(grid)
+            return installed_dds(transformation)
         return _orig_l2n(transformation)
 
     def n2l_operator(transformation):
         grid = transformation.grid
         if not transformation.origin_poly.indices_are_separate:
-            return NodeEvalOperator(grid)
+            return installed_node_eval(transformation)
         return _orig_n2l(transformation)
 
     l2n_cls = mods["minterpy.transformations.lagrange"].LagrangeToNewton

@@ -255,24 +255,65 @@ class _Transformation:
         return self.target_type(origin_poly.multi_index, coeffs, grid=origin_poly.grid)
 
 
-class DDSOperator:
+def _is_operator(x):
+    """True for anything that represents a transformation matrix: the operators below, or an
+    ``OperatorABC`` of an installed minterpy (``core/ABC/operator_abstract.py:25``)."""
+    return hasattr(x, "array_repr_full") and not hasattr(x, "shape")
+
+
+class _Operator:
+    """What the reference's ``OperatorABC`` gives its operators
+    (``core/ABC/operator_abstract.py:25-100``): the cached full matrix, the sub-matrix of the
+    active monomials, and ``op @ op`` -> the operator of the matrix product
+    (``schemes/matrix_operator.py:13-22``).  ``patch.install()`` derives the installed variants
+    from this class AND ``OperatorABC``."""
+
+    transformation = None
+    _array_repr_full = None
+
+    def _get_array_repr(self):
+        raise NotImplementedError
+
+    def _make_matrix_operator(self, matrix):
+        return MatrixOperator(matrix)
+
+    @property
+    def array_repr_full(self):
+        if self._array_repr_full is None:
+            self._array_repr_full = self._get_array_repr()
+        return self._array_repr_full
+
+    @property
+    def array_repr_sparse(self):
+        """``operator_abstract.py:82-100``: the columns of the active monomials when the
+        polynomial keeps its indices apart from the grid's, else the full matrix."""
+        full = self.array_repr_full
+        poly = getattr(self.transformation, "origin_poly", None)
+        if poly is not None and getattr(poly, "indices_are_separate", False):
+            full = full[:, poly.active_monomials]
+        return full
+
+    def _chain(self, other):
+        return self._make_matrix_operator(self.array_repr_full @ other.array_repr_full)
+
+
+class DDSOperator(_Operator):
     """Lagrange -> Newton as an operator: ``op @ coeffs`` runs the dds kernel."""
 
-    def __init__(self, grid):
+    def __init__(self, grid, transformation=None):
         self.grid = grid
-        self._full = None
+        self.transformation = transformation
 
     def __matmul__(self, other):
+        if _is_operator(other):
+            return self._chain(other)
         other_nd = other.ndim
         out = api.dds(other, self.grid.tree)
         return out.reshape(-1) if other_nd == 1 else out
 
-    @property
-    def array_repr_full(self):
+    def _get_array_repr(self):
         """The N x N matrix (dds of the identity, like ``build_l2n_matrix_dds``)."""
-        if self._full is None:
-            self._full = api.dds(np.eye(len(self.grid.multi_index)), self.grid.tree)
-        return self._full
+        return api.dds(np.eye(len(self.grid.multi_index)), self.grid.tree)
 
     def full_on_device(self, device=None):
         """The same matrix as a CUDA tensor: identity built and transformed on the device."""
@@ -282,14 +323,16 @@ class DDSOperator:
                        self.grid.tree)
 
 
-class NodeEvalOperator:
+class NodeEvalOperator(_Operator):
     """Newton -> Lagrange as an operator: evaluation at the unisolvent nodes."""
 
-    def __init__(self, grid):
+    def __init__(self, grid, transformation=None):
         self.grid = grid
-        self._full = None
+        self.transformation = transformation
 
     def __matmul__(self, other):
+        if _is_operator(other):
+            return self._chain(other)
         nodes = self.grid.unisolvent_nodes
         if _is_torch(other):
             import torch
@@ -299,14 +342,11 @@ class NodeEvalOperator:
         out = get_plan(e, gp).eval(nodes, c2)
         return out.reshape(-1) if other.ndim == 1 else out
 
-    @property
-    def array_repr_full(self):
+    def _get_array_repr(self):
         """The N x N matrix of monomial values at the nodes (``transformations/utils.py:35-55``)."""
-        if self._full is None:
-            self._full = api.eval_newton_monomials(self.grid.unisolvent_nodes,
-                                                   self.grid.multi_index.exponents,
-                                                   self.grid.generating_points, triangular=True)
-        return self._full
+        return api.eval_newton_monomials(self.grid.unisolvent_nodes,
+                                         self.grid.multi_index.exponents,
+                                         self.grid.generating_points, triangular=True)
 
     def full_on_device(self, device=None):
         """The same matrix as a CUDA tensor."""
@@ -317,14 +357,17 @@ class NodeEvalOperator:
                                          self.grid.generating_points, triangular=True)
 
 
-class MatrixOperator:
+class MatrixOperator(_Operator):
     """A dense operator (``schemes/matrix_operator.py:10-26``): ``op @ coeffs`` is one pass of
     ``mpx_apply_dense`` over the matrix, which stays on the device; ``op @ op`` gives the
-    operator of the matrix product."""
+    operator of the matrix product.  ``lower_triangular=True`` (every Lagrange<->Newton matrix of
+    a sorted index set, ``transformations/utils.py:35-55``) lets the kernel skip the zero half."""
 
-    def __init__(self, matrix):
+    def __init__(self, matrix, lower_triangular=False, transformation=None):
         self._host = None if _is_torch(matrix) else np.ascontiguousarray(matrix, dtype=np.float64)
         self._dev = matrix.contiguous() if _is_torch(matrix) else None
+        self.lower_triangular = bool(lower_triangular)
+        self.transformation = transformation
 
     def _on_device(self):
         if self._dev is None:
@@ -332,15 +375,19 @@ class MatrixOperator:
             self._dev = torch.as_tensor(self._host, device="cuda")
         return self._dev
 
-    @property
-    def array_repr_full(self):
+    def full_on_device(self, device=None):
+        """The matrix as a CUDA tensor (on `device` if given)."""
+        T = self._on_device()
+        return T if device is None else T.to(device)
+
+    def _get_array_repr(self):
         if self._host is None:
             self._host = self._dev.cpu().numpy()
         return self._host
 
     def __matmul__(self, other):
-        if isinstance(other, (MatrixOperator, DDSOperator, NodeEvalOperator)):
-            return MatrixOperator(self.array_repr_full @ other.array_repr_full)
+        if _is_operator(other):
+            return self._chain(other)
         import torch
         T = self._on_device()
         as_numpy = not _is_torch(other)
@@ -369,10 +416,10 @@ class LagrangeToNewton(_Transformation):
         (``transformations/utils.py:155-179``), the dense inverse of the Newton->Lagrange matrix
         (the monomials at the unisolvent nodes), built and inverted on the device."""
         if self.grid.multi_index.is_complete:
-            return DDSOperator(self.grid)
+            return DDSOperator(self.grid, self)
         import torch
         n2l = NodeEvalOperator(self.grid).full_on_device()
-        return MatrixOperator(torch.linalg.inv(n2l))
+        return MatrixOperator(torch.linalg.inv(n2l), transformation=self)
 
 
 class NewtonToLagrange(_Transformation):
@@ -380,7 +427,7 @@ class NewtonToLagrange(_Transformation):
     target_type = LagrangePolynomial
 
     def _get_transformation_operator(self):
-        return NodeEvalOperator(self.grid)
+        return NodeEvalOperator(self.grid, self)
 
 
 class InterpolationError(Exception):
