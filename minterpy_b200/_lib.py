@@ -39,6 +39,11 @@ DEBUG_SIGNATURES = {
                                   ctypes.POINTER(c_i64)]),
     "mpx_debug_tile_program": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, ctypes.POINTER(c_i64),
                                        ctypes.POINTER(c_i64)]),
+    # test hooks: kernel choice that the library otherwise makes by itself (no environment
+    # variable changes what the shipped library runs)
+    "mpx_debug_set_tmma": (None, [c_int]),          # at plan creation: 0 auto, 1 force, 2 never
+    "mpx_debug_set_dds_group": (None, [c_int]),     # dds through the fused slice kernel
+    "mpx_debug_set_eval_stages": (None, [c_int]),   # ring depth of the tree kernel (0 = default)
 }
 
 MPX_OK, MPX_ERR_ARG, MPX_ERR_INCOMPLETE, MPX_ERR_CUDA, MPX_ERR_UNSUPPORTED, MPX_ERR_NOMEM = range(6)

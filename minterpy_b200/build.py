@@ -21,7 +21,9 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, tuning=False):
+    """tuning=True (`python -m minterpy_b200.build --tuning`) compiles the lab-bench knobs and the
+    measured-and-dropped kernel variants in (-DMPX_TUNING); the shipped library has neither."""
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     os.makedirs(OBJ, exist_ok=True)
     headers = [os.path.join(CSRC, "mpx_common.h"), os.path.join(CSRC, "mpx_ptx.h"),
@@ -31,7 +33,8 @@ def build(force=False, verbose=False):
         s = os.path.join(CSRC, src)
         o = os.path.join(OBJ, src.replace(".cu", ".o"))
         if force or _stale(o, [s] + headers):
-            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+            cmd = ([nvcc] + NVCC_FLAGS + (["-DMPX_TUNING"] if tuning else []) +
+                   (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o])
             jobs.append(cmd)
 
     def run(cmd):
@@ -50,4 +53,5 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv or "--tuning" in sys.argv, verbose="-v" in sys.argv,
+                tuning="--tuning" in sys.argv))

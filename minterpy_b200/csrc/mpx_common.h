@@ -19,6 +19,7 @@ constexpr int MPX_COEF_CAP = 1024;    // coefficient slots (doubles) per chunk a
 constexpr int MPX_STAGES = 8;         // shared-memory ring depth of the chunk stream
 constexpr int MPX_MAX_L0 = 66;        // dimension-0 table entries a thread can hold in registers
 constexpr int MPX_MAX_M = 16;
+constexpr int MPX_DDS_REG_LEN = 16;   // longest fiber the register-resident dds kernel takes
 constexpr int MPX_DDS_COLS = 32;      // value columns per CTA of the fused dds kernel
 constexpr int MPX_DDS_MERGE_ROWS = 112; // small slices are merged until a CTA owns this many rows
 constexpr int MPX_DDS_MAX_ROWS = 736; // rows of a slice that fit shared memory (x 32 columns x 8 B)
@@ -89,6 +90,19 @@ struct DdsDim {
     int32_t *d_wrows = nullptr; // rows of those fibers
     double *d_dy = nullptr;     // (L x L) pairs (divisor, reciprocal or 0), 2 doubles each
     double *d_gcol = nullptr;   // (L) generating points of this dimension
+    // several-columns-per-lane kernel (max_len <= 40): (divisor, reciprocal) pairs as d_dy, except
+    // that a divisor whose significand is all ones -- 2^j (1 - 2^-53) up to sign, where the
+    // reciprocal-and-correct division is not exact -- is replaced by the pair (+-2^j, +-2^-j) and
+    // flagged in d_fmask (bit r of word l): its quotient is the next double after a / 2^j, away
+    // from zero (see mpx_dds.cu).  cols_ok: every divisor is ordinary or of that kind.
+    double *d_dy2 = nullptr;
+    unsigned long long *d_fmask = nullptr;
+    bool cols_ok = false;
+    // register-fiber kernel (max_len <= MPX_DDS_REG_LEN): the pairs (divisor, reciprocal or 0)
+    // for 0 <= l < r < max_len at [r (r - 1) / 2 + l], handed to the kernel as a parameter so
+    // that every table entry is an immediate constant-bank operand of the FP64 instructions
+    std::vector<double> h_pairs;
+    bool all_fast = false;      // every divisor of this dimension qualifies for the fast division
 };
 
 // A group of consecutive dimensions [lo, hi] that the divided-difference kernel handles in
@@ -113,6 +127,19 @@ struct DdsGroup {
     int32_t *d_slice_off = nullptr; // n_slices + 1
     int32_t *d_slice_rows = nullptr;// N: global row of every slice element
     std::vector<DdsGroupDim> dims;  // hi first
+};
+
+// One packed-coefficient image in device memory and what orders its users on the device.
+// The evaluation kernels read the image long after the entry point has returned, so before the
+// next call repacks it on ANOTHER stream it waits for `busy`, the event recorded behind the last
+// kernel that read it (same stream: stream order already does it).
+struct MpxImage {
+    double *ptr = nullptr;
+    size_t bytes = 0;
+    bool fixed = false;              // caller-provided storage of fixed size: never grown or freed
+    cudaEvent_t busy = nullptr;      // created on first use (not for fixed images)
+    cudaStream_t last_stream = nullptr;
+    bool in_use = false;             // `busy` has been recorded at least once
 };
 
 struct mpx_plan {
@@ -141,15 +168,25 @@ struct mpx_plan {
     std::vector<DdsGroup> dds_groups; // fused passes, top dimensions first (only if complete)
     bool dds_fast_div = true;         // every divisor qualifies for the reciprocal + correction division
     int64_t dds_updates = 0;
-    // growable scratch (packed coefficients of the current evaluation call)
-    std::mutex mu;
-    double *d_scratch = nullptr;
-    size_t scratch_bytes = 0;
-    // staging for the host-buffer entry points: two streams, two point/value blocks
+    // packed coefficients of the evaluation call in flight, one image per way in: the
+    // device-pointer entry point (mpx_eval, mpx_eval_deriv) and the host-buffer entry point each
+    // own one, so a NumPy call can never repack what a tensor call is still reading
+    std::mutex mu;                   // host-side state of `image` (pointer, size, event)
+    MpxImage image;                  // mpx_eval / mpx_eval_deriv
+    std::mutex host_mu;              // one host-buffer call per plan at a time (held to the end)
+    MpxImage host_image;             // mpx_eval_host
+    // staging for the host-buffer entry points: two streams, device blocks for points and
+    // values, page-locked blocks for callers whose arrays are pageable, the dds value array
     cudaStream_t h_stream[2] = {nullptr, nullptr};
     cudaEvent_t h_event = nullptr;
+    cudaEvent_t h_done[2] = {nullptr, nullptr};       // block b's D2H has finished
+    cudaEvent_t h_up[2] = {nullptr, nullptr};         // block b's H2D has finished
     double *h_x[2] = {nullptr, nullptr}, *h_o[2] = {nullptr, nullptr}, *h_c = nullptr;
     size_t h_x_cap[2] = {0, 0}, h_o_cap[2] = {0, 0}, h_c_cap = 0;   // bytes
+    double *p_x[2] = {nullptr, nullptr}, *p_o[2] = {nullptr, nullptr};   // page-locked host blocks
+    size_t p_x_cap[2] = {0, 0}, p_o_cap[2] = {0, 0};
+    double *h_v = nullptr;           // dds_host: the value array on the device
+    size_t h_v_cap = 0;
 };
 
 // error plumbing --------------------------------------------------------------------------
@@ -186,27 +223,34 @@ struct DeviceGuard {
 };
 
 // kernels' host launchers (defined in the .cu files) ---------------------------------------
-int mpx_launch_eval(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+// All evaluation launchers: `img` receives the packed coefficients (coeffs != nullptr) and is
+// what the kernel reads; coeffs == nullptr means `img` already holds these k polynomials.
+int mpx_launch_eval(mpx_plan *plan, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,
                     const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                     cudaStream_t stream);
 int mpx_launch_monomials(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
                          double *out, int64_t ld_out, int triangular, cudaStream_t stream);
 int mpx_launch_dds(mpx_plan *plan, double *vals, int k, int64_t ld, cudaStream_t stream);
-int mpx_ensure_scratch(mpx_plan *plan, size_t bytes);
+// make room for `bytes` in the image and order `stream` behind the image's last reader
+int mpx_image_acquire(MpxImage *img, size_t bytes, cudaStream_t stream);
+// record that work reading the image has just been enqueued on `stream`
+int mpx_image_release(MpxImage *img, cudaStream_t stream);
+void mpx_image_destroy(MpxImage *img);
 // tensor-core (many polynomials) evaluation path, mpx_eval_mma.cu
 bool mpx_mma_eligible(const mpx_plan *plan, int k);
 int mpx_mma_min_k(const mpx_plan *plan);      // smallest k that prefers this kernel to the tree kernel
 size_t mpx_mma_scratch_bytes(const mpx_plan *plan, int k);
 // orders_h (m entries, host) != nullptr: evaluate the partial derivative of those orders
-int mpx_launch_eval_mma(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+int mpx_launch_eval_mma(mpx_plan *plan, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,
                         const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                         cudaStream_t stream, const int *orders_h = nullptr);
 bool mpx_mma_fits(const mpx_plan *plan, int k);   // the tables of this index set fit shared memory
 // tensor-core tree kernel (complete sets, few polynomials), mpx_eval_tmma.cu
 bool mpx_tmma_eligible(const mpx_plan *plan, int k);
 size_t mpx_tmma_scratch_bytes(const mpx_plan *plan, int k);
-int mpx_launch_eval_tmma(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
+int mpx_launch_eval_tmma(mpx_plan *plan, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,
                          const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                          cudaStream_t stream);
+extern int mpx_test_eval_stages;   // test hook, mpx_eval.cu
 // bytes of plan scratch an evaluation of k polynomials needs (either path)
 size_t mpx_eval_scratch_bytes(const mpx_plan *plan, int k);

@@ -14,6 +14,7 @@
 #include <cstring>
 
 #include "mpx_common.h"
+#include "mpx_ptx.h"
 
 namespace {
 
@@ -394,13 +395,419 @@ dds_fiber_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_t *__
         vals[(int64_t)rows[r] * ld + col] = b[r * MPX_DDS_COLS];
 }
 
+
+// ---- one warp per fiber, several value columns per lane ------------------------------------
+// Same scheme as dds_fiber_kernel, but a lane owns C = 2H value columns (H pairs of neighbouring
+// columns, 16-byte accesses everywhere).  On this GPU a shared-memory load costs the FP64 pipe
+// about as much as two to three FP64 instructions (tools/lds_dfma_probe.cu), and an update is
+// only four of them: with one column per lane the (divisor, reciprocal) pair and the pivot value
+// cost more than the arithmetic.  Here one pair serves C updates and one pivot load two, index
+// loads and address arithmetic are shared by C columns, and the rare cases the fast division
+// cannot take no longer branch inside the sweep: every update computes the fast quotient and ORs
+// "not valid" into one sticky flag per lane; a flagged lane redoes its columns with true
+// divisions from the values still unchanged in global memory (dds_redo_columns).
+// Buffer layout: row r, pair h of the lane at double2 index (r * H + h) * 32 + lane.
+template <int H>
+__device__ __noinline__ void dds_redo_columns(double2 *__restrict__ bl, const double *__restrict__ vals,
+                                              int64_t ld, int64_t col0, unsigned active,
+                                              const int32_t *__restrict__ rows, int len,
+                                              const double *__restrict__ gcol)
+{
+    for (int r = 0; r < len; ++r)
+#pragma unroll
+        for (int h = 0; h < H; ++h)
+            if (active >> h & 1)
+                bl[(r * H + h) * 32] = *reinterpret_cast<const double2 *>(vals + (int64_t)rows[r] * ld + col0 + 64 * h);
+    for (int i = 1; i < len; ++i)
+        for (int r = i; r < len; ++r) {
+            const double d = __dsub_rn(gcol[r], gcol[i - 1]);   // the subtraction the host tabulated
+#pragma unroll
+            for (int h = 0; h < H; ++h) {
+                double2 x = bl[(r * H + h) * 32];
+                const double2 pv = bl[((i - 1) * H + h) * 32];
+                x.x = __ddiv_rn(__dsub_rn(x.x, pv.x), d);
+                x.y = __ddiv_rn(__dsub_rn(x.y, pv.y), d);
+                bl[(r * H + h) * 32] = x;
+            }
+        }
+}
+
+// Division by a table divisor d with y = RN(1/d):  q = a y;  r = fma(-d, q, a);  q' = fma(r, y, q)
+// is the IEEE quotient unless d's significand is all ones (see the fused kernel above).  Such a
+// divisor is d = s 2^j (1 - 2^-53), s = +-1 (between Chebyshev points: 1 - 6e-17), and then
+//     a / d = A (1 + 2^-53 + 2^-106 + ...),   A = a / (s 2^j)   (exact),
+// lies strictly between |A| + ulp/2 and |A| + ulp for every normal A: the quotient is the next
+// double after A, away from zero.  The plan stores (s 2^j, s 2^-j) for these entries, with which
+// the same three instructions return exactly A, and flags them (INC); one integer increment of
+// the bit pattern finishes the division.  tools/div_check.cu compares both forms with __ddiv_rn.
+// `bad` collects what neither form may take: a outside [2^-900, 2^900) other than +0.
+template <bool FLAGGED>
+__device__ __forceinline__ double dds_update_flag(double x, double pv, double d, double y, bool inc,
+                                                  bool &bad)
+{
+    const double a = __dsub_rn(x, pv);
+    const double q = __dmul_rn(a, y);
+    const double r = __fma_rn(-d, q, a);
+    double q2 = __fma_rn(r, y, q);
+    const int hi = __double2hiint(a);
+    const bool in_range = ((unsigned)(hi & 0x7ff00000) - (123u << 20)) < (1800u << 20);
+    const bool plus_zero = (hi | __double2loint(a)) == 0;
+    bad = bad || !(in_range || plus_zero);
+    if constexpr (FLAGGED) {
+        if (inc && !plus_zero)
+            q2 = __longlong_as_double(__double_as_longlong(q2) + 1);
+    }
+    return q2;
+}
+
+template <int FW, int H>
+__global__ void __launch_bounds__(FW * 32)
+dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_t *__restrict__ woff,
+                      const int32_t *__restrict__ wrows, int n_work, const double *__restrict__ dy,
+                      const unsigned long long *__restrict__ fmask, const double *__restrict__ gcol, int L)
+{
+    extern __shared__ __align__(16) unsigned char fsm[];
+    double2 *dy2 = reinterpret_cast<double2 *>(fsm);                  // (divisor, reciprocal), L x L
+    // flag words behind the fiber buffers and the barriers: bit r of word l = entry (l, r) flagged
+    unsigned long long *fm = reinterpret_cast<unsigned long long *>(dy2 + L * L + (size_t)FW * L * H * 32) + FW;
+    for (int i = threadIdx.x; i < L * L; i += blockDim.x) dy2[i] = reinterpret_cast<const double2 *>(dy)[i];
+    for (int i = threadIdx.x; i < L; i += blockDim.x) fm[i] = fmask[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int f = blockIdx.x * FW + warp;
+    if (f >= n_work) return;
+    constexpr int C = 2 * H;
+    const int64_t col0 = (int64_t)blockIdx.y * (32 * C) + 2 * lane;      // pair h starts at col0 + 64 h
+    unsigned active = 0;
+#pragma unroll
+    for (int h = 0; h < H; ++h) active |= (col0 + 64 * h < k) ? 1u << h : 0u;
+    if (!active) return;
+    const int o = woff[f];
+    const int len = woff[f + 1] - o;
+    const int32_t *rows = wrows + o;
+    double2 *bw = dy2 + L * L + (size_t)warp * L * H * 32;               // this warp's fiber buffer
+    double2 *bl = bw + lane;                                             // this lane's slots
+    // Gather: row r of the fiber is ONE contiguous piece of global memory (the warp's 64 H value
+    // columns), and the buffer keeps it contiguous too, so lane r hands the whole row to the TMA
+    // (cp.async.bulk, completion counted on the warp's mbarrier): every row of the fiber is in
+    // flight at once, no registers and no address arithmetic per element.
+    const int64_t cw0 = (int64_t)blockIdx.y * (32 * C);                  // first column of the warp
+    const int ncols = (int)((k - cw0 < 32 * C) ? (k - cw0) : 32 * C);    // even: k is
+    const uint32_t row_bytes = (uint32_t)ncols * 8u;
+    uint64_t *bar = reinterpret_cast<uint64_t *>(dy2 + L * L + (size_t)FW * L * H * 32) + warp;
+    if (lane == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (ncols < 32 * C)                                  // ragged last column block: the sweep
+        for (int r = 0; r < len; ++r)                    // must not chew on stale shared memory
+#pragma unroll
+            for (int h = 0; h < H; ++h) bl[(r * H + h) * 32] = make_double2(0.0, 0.0);
+    if (ncols < 32 * C) fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive_expect_tx(bar, row_bytes * (uint32_t)len);
+    for (int r = lane; r < len; r += 32)
+        bulk_g2s(bw + (size_t)r * H * 32, vals + (int64_t)rows[r] * ld + cw0, row_bytes, bar);
+    mbar_wait(bar, 0);
+    bool bad = false;
+    // Row-blocked sweep (see dds_fiber_kernel): element r receives its updates i = 1..r in order,
+    // each with the final value of element i-1; four rows advance together.
+#ifdef MPX_DDS_PROBE_NO_SWEEP
+    int r = len;
+#else
+    int r = 1;
+#endif
+    const int first_block = 1 + ((len - 1) & 3);
+    for (; r < first_block; ++r) {
+        double2 x[H];
+#pragma unroll
+        for (int h = 0; h < H; ++h) x[h] = bl[(r * H + h) * 32];
+        const double2 *t = dy2 + r;
+        const double2 *vp = bl;
+#pragma unroll 1
+        for (int i = 1; i <= r; ++i) {
+            const double2 t0 = t[0];
+            const bool inc = (fm[i - 1] >> r) & 1ull;
+#pragma unroll
+            for (int h = 0; h < H; ++h) {
+                const double2 pv = vp[h * 32];
+                x[h].x = dds_update_flag<true>(x[h].x, pv.x, t0.x, t0.y, inc, bad);
+                x[h].y = dds_update_flag<true>(x[h].y, pv.y, t0.x, t0.y, inc, bad);
+            }
+            t += L;
+            vp += H * 32;
+        }
+#pragma unroll
+        for (int h = 0; h < H; ++h) bl[(r * H + h) * 32] = x[h];
+    }
+    for (; r + 3 < len; r += 4) {
+        double2 x[4][H];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int h = 0; h < H; ++h) x[q][h] = bl[((r + q) * H + h) * 32];
+        const double2 *t = dy2 + r;               // entries (i-1, r..r+3), i-1 = 0
+        const double2 *vp = bl;
+#pragma unroll 1
+        for (int i = 1; i <= r; ++i) {
+            double2 tq[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) tq[q] = t[q];
+            const unsigned flags = (unsigned)(fm[i - 1] >> r) & 15u;     // uniform: table data
+            if (flags == 0) {
+#pragma unroll
+                for (int h = 0; h < H; ++h) {
+                    const double2 pv = vp[h * 32];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        x[q][h].x = dds_update_flag<false>(x[q][h].x, pv.x, tq[q].x, tq[q].y, false, bad);
+                        x[q][h].y = dds_update_flag<false>(x[q][h].y, pv.y, tq[q].x, tq[q].y, false, bad);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int h = 0; h < H; ++h) {
+                    const double2 pv = vp[h * 32];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const bool inc = (flags >> q) & 1u;
+                        x[q][h].x = dds_update_flag<true>(x[q][h].x, pv.x, tq[q].x, tq[q].y, inc, bad);
+                        x[q][h].y = dds_update_flag<true>(x[q][h].y, pv.y, tq[q].x, tq[q].y, inc, bad);
+                    }
+                }
+            }
+            t += L;
+            vp += H * 32;
+        }
+        // the last three updates of rows r+1..r+3 use the rows of the block itself
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {             // pivot row r + j, table row r + j
+#pragma unroll
+            for (int q = j + 1; q < 4; ++q) {
+                const double2 tp = t[q];
+                const bool inc = (fm[r + j] >> (r + q)) & 1ull;
+#pragma unroll
+                for (int h = 0; h < H; ++h) {
+                    x[q][h].x = dds_update_flag<true>(x[q][h].x, x[j][h].x, tp.x, tp.y, inc, bad);
+                    x[q][h].y = dds_update_flag<true>(x[q][h].y, x[j][h].y, tp.x, tp.y, inc, bad);
+                }
+            }
+            t += L;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int h = 0; h < H; ++h) bl[((r + q) * H + h) * 32] = x[q][h];
+    }
+#ifndef MPX_DDS_PROBE_NO_REDO
+    if (bad) dds_redo_columns<H>(bl, vals, ld, col0, active, rows, len, gcol);
+#endif
+    // Write back rows 1..len-1 (element 0 of a fiber never changes), again one bulk copy per row
+    fence_proxy_async_smem();
+    __syncwarp();
+    for (int rr = 1 + lane; rr < len; rr += 32)
+        bulk_s2g(vals + (int64_t)rows[rr] * ld + cw0, bw + (size_t)rr * H * 32, row_bytes);
+    bulk_commit_and_wait_read();          // the buffer must outlive the copies that read it
+}
+
+// ---- register-resident fibers (all fibers of the dimension at most MPX_DDS_REG_LEN long) -------
+// One warp per fiber, lane = value column, one pass per dimension like the kernel above, but the
+// fiber never touches shared memory: a lane keeps its column of the fiber in registers, the code
+// for every fiber length is fully unrolled, and the (divisor, reciprocal) pairs arrive as a
+// kernel PARAMETER -- with static indices every table entry is an immediate constant-bank
+// operand of the DADD/DMUL/DFMA that uses it, so an update issues its four FP64 instructions and
+// the range test, nothing else.  (On this GPU every shared-memory load costs the FP64 pipe about
+// as much as two DFMAs -- tools/lds_dfma_probe.cu -- and the kernel above needs 1.25 of them per
+// update.)  Element r receives its updates i = 1..r in order with the final value of element
+// i-1, as in the reference; for a fixed i the updates of r = i..len-1 are independent chains.
+struct DdsPairs {
+    double2 t[MPX_DDS_REG_LEN * (MPX_DDS_REG_LEN - 1) / 2];    // (l, r) at [r (r - 1) / 2 + l]
+};
+
+// The rare cases the fast division cannot take (numerator zero-but-not-plus-zero, subnormal,
+// huge, inf, nan; a divisor whose reciprocal was not tabulated) do not branch inside the unrolled
+// code: every update computes the fast quotient and ORs "this one was not valid" into one sticky
+// predicate; a lane whose predicate is set at the end throws its fiber away and redoes it here
+// with true divisions, from the values still unchanged in global memory.
+__device__ __noinline__ void dds_fiber_slow(double *__restrict__ vals, int64_t ld, int col,
+                                            const int32_t *__restrict__ rows, int len,
+                                            const double2 *__restrict__ tab)
+{
+    for (int r = 1; r < len; ++r) {
+        double *pr = vals + (int64_t)rows[r] * ld + col;
+        double x = *pr;
+        for (int i = 1; i <= r; ++i) {
+            // rows below r already hold their final values (written by this loop)
+            const double pv = vals[(int64_t)rows[i - 1] * ld + col];
+            x = __ddiv_rn(__dsub_rn(x, pv), tab[r * (r - 1) / 2 + (i - 1)].x);
+        }
+        *pr = x;
+    }
+}
+
+template <bool CHECK_Y>
+__device__ __forceinline__ double dds_update_const(double x, double pv, double d, double y, bool &bad)
+{
+    const double a = __dsub_rn(x, pv);
+    const double q = __dmul_rn(a, y);
+    const double r = __fma_rn(-d, q, a);
+    const double q2 = __fma_rn(r, y, q);
+    const int hi = __double2hiint(a);
+    // valid when 2^-900 <= |a| < 2^900, or a is +0 (x == pv: the sequence returns the correctly
+    // signed zero), and the divisor qualified (its tabulated reciprocal is not 0)
+    const bool in_range = ((unsigned)(hi & 0x7ff00000) - (123u << 20)) < (1800u << 20);
+    const bool plus_zero = (hi | __double2loint(a)) == 0;
+    bad = bad || !(in_range || plus_zero);
+    if constexpr (CHECK_Y) bad = bad || __double2hiint(y) == 0;
+    return q2;
+}
+
+template <int LEN, bool CHECK_Y>
+__device__ __forceinline__ void dds_fiber_in_registers(double *__restrict__ vals, int64_t ld, int col,
+                                                       const int32_t *__restrict__ rows,
+                                                       const DdsPairs &tab)
+{
+    double *p[LEN];
+    double v[LEN];
+#pragma unroll
+    for (int r = 0; r < LEN; ++r) p[r] = vals + (int64_t)rows[r] * ld + col;
+#pragma unroll
+    for (int r = 0; r < LEN; ++r) v[r] = *p[r];
+    bool bad = false;
+#pragma unroll
+    for (int i = 1; i < LEN; ++i) {
+#pragma unroll
+        for (int r = i; r < LEN; ++r) {
+#ifdef MPX_DDS_PROBE_ONE_PAIR
+            const double2 t = tab.t[0];
+#else
+            const double2 t = tab.t[r * (r - 1) / 2 + (i - 1)];
+#endif
+            v[r] = dds_update_const<CHECK_Y>(v[r], v[i - 1], t.x, t.y, bad);
+        }
+    }
+    if (bad) {
+        dds_fiber_slow(vals, ld, col, rows, LEN, tab.t);
+        return;
+    }
+#pragma unroll
+    for (int r = 1; r < LEN; ++r) *p[r] = v[r];          // element 0 of a fiber never changes
+}
+
+template <bool CHECK_Y, int FW>
+__global__ void __launch_bounds__(FW * 32)
+dds_fiber_reg_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_t *__restrict__ woff,
+                     const int32_t *__restrict__ wrows, int n_work,
+                     const __grid_constant__ DdsPairs tab)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int f = blockIdx.x * FW + warp;
+    const int col = blockIdx.y * MPX_DDS_COLS + lane;
+    if (f >= n_work || col >= k) return;
+    const int o = woff[f];
+    const int len = woff[f + 1] - o;
+    const int32_t *rows = wrows + o;
+    switch (len) {
+#define MPX_DDS_LEN(L) case L: dds_fiber_in_registers<L, CHECK_Y>(vals, ld, col, rows, tab); break;
+        MPX_DDS_LEN(2) MPX_DDS_LEN(3) MPX_DDS_LEN(4) MPX_DDS_LEN(5) MPX_DDS_LEN(6) MPX_DDS_LEN(7)
+        MPX_DDS_LEN(8) MPX_DDS_LEN(9) MPX_DDS_LEN(10) MPX_DDS_LEN(11) MPX_DDS_LEN(12)
+        MPX_DDS_LEN(13) MPX_DDS_LEN(14) MPX_DDS_LEN(15) MPX_DDS_LEN(16)
+#undef MPX_DDS_LEN
+    default: break;
+    }
+}
+
 }  // namespace
+
+// several columns per lane: k, ld and the base address must allow 16-byte accesses, fibers <= 40
+template <int H, int FW = 4>
+static int launch_dds_cols_h(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
+                             bool *handled)
+{
+    int smem_max = 0;
+    MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
+    *handled = false;
+    auto smem_of = [&](const DdsDim &dd) {
+        return ((size_t)2 * dd.max_len * dd.max_len + (size_t)FW * dd.max_len * 64 * H + FW + dd.max_len) * sizeof(double);
+    };
+    for (int d = 0; d < pl->m; ++d) {
+        const DdsDim &dd = pl->dds[d];
+        if (dd.n_work == 0) continue;
+        if (dd.max_len > 40 || !dd.cols_ok || smem_of(dd) > (size_t)smem_max) return MPX_OK;
+    }
+    auto fn = dds_fiber_cols_kernel<FW, H>;
+    MPX_CUDA(mpx_allow_max_smem(fn));
+    // (Running all passes over one L2-sized group of columns before the next group was measured:
+    // 3 % slower at cfg4 -- the passes are not bound by HBM alone, and smaller launches have
+    // longer tails.)
+    for (int d = pl->m - 1; d >= 0; --d) {
+        const DdsDim &dd = pl->dds[d];
+        if (dd.n_work == 0) continue;
+        dim3 grid((unsigned)((dd.n_work + FW - 1) / FW), (unsigned)((k + 64 * H - 1) / (64 * H)), 1);
+        fn<<<grid, FW * 32, smem_of(dd), stream>>>(vals, ld, k, dd.d_woff, dd.d_wrows, dd.n_work,
+                                                   dd.d_dy2, dd.d_fmask, dd.d_gcol, dd.max_len);
+        MPX_CUDA(cudaGetLastError());
+    }
+    *handled = true;
+    return MPX_OK;
+}
+
+static int launch_dds_cols(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
+                           bool *handled)
+{
+    *handled = false;
+    if ((k & 1) || (ld & 1) || (reinterpret_cast<uintptr_t>(vals) & 15) || k < 64) return MPX_OK;
+#ifdef MPX_TUNING
+    static const int fw = getenv("MPX_DDS_COLS_FW") ? atoi(getenv("MPX_DDS_COLS_FW")) : 4;
+    static const int hh = getenv("MPX_DDS_COLS_H") ? atoi(getenv("MPX_DDS_COLS_H")) : 0;
+    if (hh == 1 || (hh == 0 && k < 128)) {
+        if (fw == 2) return launch_dds_cols_h<1, 2>(pl, vals, k, ld, stream, handled);
+        if (fw == 8) return launch_dds_cols_h<1, 8>(pl, vals, k, ld, stream, handled);
+        return launch_dds_cols_h<1, 4>(pl, vals, k, ld, stream, handled);
+    }
+    if (fw == 2) return launch_dds_cols_h<2, 2>(pl, vals, k, ld, stream, handled);
+    if (fw == 8) return launch_dds_cols_h<2, 8>(pl, vals, k, ld, stream, handled);
+    return launch_dds_cols_h<2, 4>(pl, vals, k, ld, stream, handled);
+#else
+    if (k >= 128) return launch_dds_cols_h<2>(pl, vals, k, ld, stream, handled);
+    return launch_dds_cols_h<1>(pl, vals, k, ld, stream, handled);
+#endif
+}
+
+// register-resident fibers: every dimension with work must have max_len <= MPX_DDS_REG_LEN
+static int launch_dds_registers(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
+                                bool *handled)
+{
+    *handled = false;
+    for (int d = 0; d < pl->m; ++d)
+        if (pl->dds[d].n_work > 0 && pl->dds[d].h_pairs.empty()) return MPX_OK;
+    constexpr int FW = 4;
+    for (int d = pl->m - 1; d >= 0; --d) {
+        const DdsDim &dd = pl->dds[d];
+        if (dd.n_work == 0) continue;
+        DdsPairs tab;
+        static_assert(sizeof(tab) == sizeof(double) * MPX_DDS_REG_LEN * (MPX_DDS_REG_LEN - 1), "table size");
+        memcpy(&tab, dd.h_pairs.data(), sizeof(tab));
+        dim3 grid((unsigned)((dd.n_work + FW - 1) / FW), (unsigned)((k + MPX_DDS_COLS - 1) / MPX_DDS_COLS), 1);
+        if (dd.all_fast)
+            dds_fiber_reg_kernel<false, FW><<<grid, FW * 32, 0, stream>>>(vals, ld, k, dd.d_woff, dd.d_wrows, dd.n_work, tab);
+        else
+            dds_fiber_reg_kernel<true, FW><<<grid, FW * 32, 0, stream>>>(vals, ld, k, dd.d_woff, dd.d_wrows, dd.n_work, tab);
+        MPX_CUDA(cudaGetLastError());
+    }
+    *handled = true;
+    return MPX_OK;
+}
 
 template <int FW>
 static int launch_dds_fibers_fw(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
                                 bool *handled)
 {
+#ifdef MPX_TUNING
     static const bool force_div = getenv("MPX_DDS_TRUE_DIV") != nullptr;
+#else
+    constexpr bool force_div = false;
+#endif
     int smem_max = 0;
     MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
     *handled = false;
@@ -438,13 +845,18 @@ static int launch_dds_fibers(mpx_plan *pl, double *vals, int k, int64_t ld, cuda
     // 7 % faster at cfg4); long fibers want fewer, larger buffers per CTA
     int longest = 0;
     for (int d = 0; d < pl->m; ++d) longest = std::max(longest, pl->dds[d].max_len);
+#ifdef MPX_TUNING
     static const int forced = getenv("MPX_DDS_FIBER_WARPS") ? atoi(getenv("MPX_DDS_FIBER_WARPS")) : 0;
+#else
+    constexpr int forced = 0;
+#endif
     const int fw = forced ? forced : (longest <= 16 || longest > 64) ? 4 : 8;
     if (fw == 4) return launch_dds_fibers_fw<4>(pl, vals, k, ld, stream, handled);
     if (fw == 16) return launch_dds_fibers_fw<16>(pl, vals, k, ld, stream, handled);
     return launch_dds_fibers_fw<8>(pl, vals, k, ld, stream, handled);
 }
 
+#ifdef MPX_TUNING
 static int launch_dds_per_dim(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream)
 {
     for (int d = pl->m - 1; d >= 0; --d) {
@@ -469,6 +881,13 @@ static int launch_dds_per_dim(mpx_plan *pl, double *vals, int k, int64_t ld, cud
     }
     return MPX_OK;
 }
+#endif
+
+// Test hook (not in the public header): 1 routes mpx_dds through the fused slice kernel, which
+// otherwise only runs for index sets whose fibers do not fit the one-warp-per-fiber kernels;
+// 2 through the shared-memory fiber kernel, which otherwise only takes fibers longer than 16.
+static int mpx_test_dds_group = 0;
+extern "C" void mpx_debug_set_dds_group(int on) { mpx_test_dds_group = on; }
 
 int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream)
 {
@@ -476,14 +895,28 @@ int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t s
         return mpx_fail(MPX_ERR_INCOMPLETE,
                         "trying to use the divided difference scheme with incomplete multi "
                         "indices, but DDS only works for complete multi indices (without 'holes').");
+    // default: one warp per fiber, one pass per dimension; the fused slice kernel takes over
+    // when a fiber buffer does not fit shared memory (and, in a -DMPX_TUNING build, on request)
+#ifdef MPX_TUNING
     static const bool per_dim = getenv("MPX_DDS_PER_DIM") != nullptr;   // old one-pass-per-dimension path
     if (per_dim) return launch_dds_per_dim(pl, vals, k, ld, stream);
-    // default: one warp per fiber, one pass per dimension; MPX_DDS_MODE=group selects the fused
-    // slice kernel, which also takes over when a fiber buffer does not fit shared memory
     static const char *mode = getenv("MPX_DDS_MODE");          // "fiber" | "group"
+#else
+    const char *mode = mpx_test_dds_group == 1 ? "group" : mpx_test_dds_group == 2 ? "fiber"
+                       : mpx_test_dds_group == 3 ? "registers" : nullptr;
+#endif
     if (!mode || strcmp(mode, "group") != 0) {
         bool handled = false;
-        int rc = launch_dds_fibers(pl, vals, k, ld, stream, &handled);
+        int rc = MPX_OK;
+        if (!mode) {
+            rc = launch_dds_cols(pl, vals, k, ld, stream, &handled);
+            if (rc != MPX_OK || handled) return rc;
+        }
+        if (mode && strcmp(mode, "registers") == 0) {
+            rc = launch_dds_registers(pl, vals, k, ld, stream, &handled);
+            if (rc != MPX_OK || handled) return rc;
+        }
+        rc = launch_dds_fibers(pl, vals, k, ld, stream, &handled);
         if (rc != MPX_OK || handled) return rc;
     }
     for (const DdsGroup &grp : pl->dds_groups) {
@@ -493,7 +926,11 @@ int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t s
         a.n_dims = (int)grp.dims.size();
         a.max_rows = grp.max_rows;
         size_t diff_doubles = 0, g_doubles = 0, meta_words = 0;
+#ifdef MPX_TUNING
         static const bool force_div = getenv("MPX_DDS_TRUE_DIV") != nullptr;
+#else
+        constexpr bool force_div = false;
+#endif
         bool fast = pl->dds_fast_div && !force_div;
         bool any = false;
         for (int t = 0; t < a.n_dims; ++t) {

@@ -464,15 +464,15 @@ size_t eval_smem_bytes(const mpx_plan *pl, int R, int NT, int stages)
 
 // coefficients == nullptr: the plan's scratch already holds the packed image of these k
 // polynomials (mpx_eval_host packs once, then evaluates block after block)
-int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
+int mpx_launch_eval(mpx_plan *pl, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,
                     const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                     cudaStream_t stream)
 {
     if (P == 0 && coeffs == nullptr) return MPX_OK;
     if (mpx_mma_eligible(pl, k))
-        return mpx_launch_eval_mma(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
+        return mpx_launch_eval_mma(pl, img, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
     if (mpx_tmma_eligible(pl, k))
-        return mpx_launch_eval_tmma(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
+        return mpx_launch_eval_tmma(pl, img, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
     if (!pl->tree_ok)
         return mpx_fail(MPX_ERR_UNSUPPORTED,
                         "dimension-0 exponent > 64 needs the shared-memory-table kernel, whose tables "
@@ -500,17 +500,27 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
         {66, 1, 256, kfn<66, 1, 2, 256, 1>()},
         {66, 1, 128, kfn<66, 1, 2, 128, 1>()},
         {66, 1, 64, kfn<66, 1, 2, 64, 1>()},
-        // experimental alternatives, selected with MPX_EVAL_VARIANT=<index>
+#ifdef MPX_TUNING
+        // measured and dropped; built only with -DMPX_TUNING, MPX_EVAL_VARIANT=<index>
         {18, 4, 256, kfn<18, 4, 2, 256, 1>()},   // 19: two accumulators per point
         {18, 3, 384, kfn<18, 3, 1, 384, 1>()},   // 20: 3 points, 12 warps
         {18, 2, 512, kfn<18, 2, 1, 512, 1>()},   // 21: 2 points, 16 warps in one CTA
+#endif
     };
     constexpr int n_standard = 19;
     int smem_max = 0;
     MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
-    // tuning knobs for experiments (defaults are what the library ships with)
+    // The shipped library takes no tuning input from the environment: the knobs below exist only
+    // in a -DMPX_TUNING build (lab bench) and in the ring stress test's build (MPX_TEST_HOOKS).
+#ifdef MPX_TUNING
     static const int env_variant = getenv("MPX_EVAL_VARIANT") ? atoi(getenv("MPX_EVAL_VARIANT")) : -1;
     static const int env_stages = getenv("MPX_EVAL_STAGES") ? atoi(getenv("MPX_EVAL_STAGES")) : 0;
+    static const bool no_pair = getenv("MPX_EVAL_NO_CTA_PAIR") != nullptr;
+#else
+    constexpr int env_variant = -1;
+    const int env_stages = mpx_test_eval_stages;       // 0 unless a test set it
+    const bool no_pair = mpx_test_eval_stages != 0;
+#endif
     int stages = env_stages > 0 ? env_stages : 4;
     if (stages > MPX_STAGES) stages = MPX_STAGES;
     if (stages < 2) stages = 2;
@@ -519,7 +529,6 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
     // independent CTAs of 128 threads per SM, each with a two-stage ring, than as one CTA of
     // 256: the CTAs drift apart and fill each other's gaps at leaf and record boundaries.
     // Short-leaf sets lose as much (more records per chunk, the shallow ring runs dry).
-    static const bool no_pair = getenv("MPX_EVAL_NO_CTA_PAIR") != nullptr;
     if (env_stages == 0 && !no_pair && pl->prog.n_leaves > 0 && pl->N >= 8 * pl->prog.n_leaves) {
         int sm_total = 0;
         MPX_CUDA(cudaDeviceGetAttribute(&sm_total, cudaDevAttrMaxSharedMemoryPerMultiprocessor, pl->device));
@@ -546,19 +555,19 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
     // pack the coefficients into the program image (plan scratch)
     const int64_t n_slots = (int64_t)pl->prog.n_chunks * MPX_COEF_CAP;
     if (coeffs) {
-        int rc = mpx_ensure_scratch(pl, (size_t)n_slots * k * sizeof(double));
+        int rc = mpx_image_acquire(img, (size_t)n_slots * k * sizeof(double), stream);
         if (rc != MPX_OK) return rc;
         const int64_t total = n_slots * k;
         const int tb = 256;
         pack_coeffs_kernel<<<(unsigned)((total + tb - 1) / tb), tb, 0, stream>>>(
-            coeffs, ld_c, k, pl->d_slot_src, n_slots, pl->d_scratch);
+            coeffs, ld_c, k, pl->d_slot_src, n_slots, img->ptr);
         MPX_CUDA(cudaGetLastError());
     }
-    if (P == 0) return MPX_OK;
+    if (P == 0) return coeffs ? mpx_image_release(img, stream) : MPX_OK;
 
     EvalParams prm;
     prm.xx = xx; prm.ld_xx = ld_xx; prm.P = P; prm.out = out; prm.ld_out = ld_out;
-    prm.desc = pl->d_desc; prm.coef = pl->d_scratch; prm.gp = pl->d_gp;
+    prm.desc = pl->d_desc; prm.coef = img->ptr; prm.gp = pl->d_gp;
     prm.n_chunks = pl->prog.n_chunks; prm.stages = stages; prm.m = pl->m; prm.gp_rows = pl->gp_rows;
     for (int i = 0; i < MPX_MAX_M; ++i) { prm.max_exp[i] = pl->max_exp[i]; prm.start_exp[i] = pl->start_exp[i]; }
 
@@ -570,8 +579,14 @@ int mpx_launch_eval(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
     dim3 grid((unsigned)tiles, (unsigned)k, 1);
     void *args[] = {(void *)&prm};
     MPX_CUDA(cudaLaunchKernel(v->fn, grid, dim3(nt, 1, 1), args, smem, stream));
-    return MPX_OK;
+    return mpx_image_release(img, stream);
 }
+
+// Test hook (not in the public header): ring depth of the tree kernel, 0 = the default.  The
+// ring stress test runs many-chunk programs through 2-, 3- and 4-deep rings of the one-CTA
+// variant.
+int mpx_test_eval_stages = 0;
+extern "C" void mpx_debug_set_eval_stages(int stages) { mpx_test_eval_stages = stages; }
 
 size_t mpx_eval_scratch_bytes(const mpx_plan *pl, int k)
 {

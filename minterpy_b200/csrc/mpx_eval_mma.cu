@@ -289,8 +289,10 @@ size_t mma_smem_bytes(const mpx_plan *pl, int nt8, int nw)
 // 8-column tile here, 26 vs 33 ms.
 int mpx_mma_min_k(const mpx_plan *pl)
 {
+#ifdef MPX_TUNING
     static const int env_min_k = getenv("MPX_EVAL_MMA_MIN_K") ? atoi(getenv("MPX_EVAL_MMA_MIN_K")) : 0;
     if (env_min_k > 0) return env_min_k;
+#endif
     if (pl->tree_ok && pl->prog.n_leaves > 0 && pl->N >= 6 * pl->prog.n_leaves) return 13;
     if (pl->tree_ok && pl->prog.n_leaves > 0 && pl->N < 4 * pl->prog.n_leaves) return 4;
     return 8;
@@ -317,7 +319,7 @@ bool mpx_mma_fits(const mpx_plan *pl, int k)
            mma_smem_bytes(pl, mma_nt8_for(k), 2) <= MMA_SMEM_LIMIT;
 }
 
-int mpx_launch_eval_mma(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
+int mpx_launch_eval_mma(mpx_plan *pl, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,
                         const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                         cudaStream_t stream, const int *orders_h)
 {
@@ -325,18 +327,18 @@ int mpx_launch_eval_mma(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx
     const int tiles = (k + 8 * nt8 - 1) / (8 * nt8);
     const int rs = 8 * nt8 + 4;
     if (coeffs) {
-        int rc = mpx_ensure_scratch(pl, mpx_mma_scratch_bytes(pl, k));
+        int rc = mpx_image_acquire(img, mpx_mma_scratch_bytes(pl, k), stream);
         if (rc != MPX_OK) return rc;
         const int64_t total = (int64_t)tiles * pl->mma_chunks * KC * rs;
         pack_mma_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(
-            coeffs, ld_c, k, pl->N, pl->mma_chunks, nt8, pl->d_scratch);
+            coeffs, ld_c, k, pl->N, pl->mma_chunks, nt8, img->ptr);
         MPX_CUDA(cudaGetLastError());
     }
-    if (P == 0) return MPX_OK;
+    if (P == 0) return coeffs ? mpx_image_release(img, stream) : MPX_OK;
 
     MmaParams prm;
     prm.xx = xx; prm.ld_xx = ld_xx; prm.P = P; prm.out = out; prm.ld_out = ld_out; prm.k = k;
-    prm.exp64 = pl->d_exp64; prm.coef = pl->d_scratch; prm.gp = pl->d_gp;
+    prm.exp64 = pl->d_exp64; prm.coef = img->ptr; prm.gp = pl->d_gp;
     prm.n_chunks = pl->mma_chunks; prm.m = pl->m; prm.gp_rows = pl->gp_rows;
     int e1 = 1;
     for (int i = 0; i < pl->m; ++i) { prm.max_exp[i] = pl->max_exp[i]; e1 = std::max(e1, pl->max_exp[i] + 1); }
@@ -347,8 +349,11 @@ int mpx_launch_eval_mma(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx
     const int nw = mma_smem_bytes(pl, nt8, 8) <= MMA_SMEM_LIMIT ? 8 : 2;
     const size_t smem = mma_smem_bytes(pl, nt8, nw);
     const int mp = mma_padded_dims(pl->m);
-#define MPX_MMA_CASE(NT8, NW) \
-    if (nt8 == NT8 && nw == NW) return launch_mp<NT8, NW>(mp, prm, tiles, smem, stream);
+#define MPX_MMA_CASE(NT8, NW)                                              \
+    if (nt8 == NT8 && nw == NW) {                                          \
+        int rc = launch_mp<NT8, NW>(mp, prm, tiles, smem, stream);         \
+        return rc != MPX_OK ? rc : mpx_image_release(img, stream);         \
+    }
     MPX_MMA_CASE(8, 8) MPX_MMA_CASE(8, 2) MPX_MMA_CASE(4, 8) MPX_MMA_CASE(4, 2)
     MPX_MMA_CASE(2, 8) MPX_MMA_CASE(2, 2) MPX_MMA_CASE(1, 8) MPX_MMA_CASE(1, 2)
 #undef MPX_MMA_CASE

@@ -332,6 +332,13 @@ size_t tmma_smem_bytes(const mpx_plan *pl, int pts)
 
 }  // namespace
 
+namespace {
+int tmma_done(int rc, MpxImage *img, cudaStream_t stream)
+{
+    return rc != MPX_OK ? rc : mpx_image_release(img, stream);
+}
+}  // namespace
+
 bool mpx_tmma_eligible(const mpx_plan *pl, int k)
 {
     (void)k;
@@ -343,39 +350,43 @@ size_t mpx_tmma_scratch_bytes(const mpx_plan *pl, int k)
     return (size_t)pl->tprog.n_chunks * MPX_T_COEF_CAP * (size_t)k * sizeof(double);
 }
 
-int mpx_launch_eval_tmma(mpx_plan *pl, const double *xx, int64_t P, int64_t ld_xx,
+int mpx_launch_eval_tmma(mpx_plan *pl, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,
                          const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                          cudaStream_t stream)
 {
     const int64_t n_slots = (int64_t)pl->tprog.n_chunks * MPX_T_COEF_CAP;
     if (coeffs) {
-        int rc = mpx_ensure_scratch(pl, mpx_tmma_scratch_bytes(pl, k));
+        int rc = mpx_image_acquire(img, mpx_tmma_scratch_bytes(pl, k), stream);
         if (rc != MPX_OK) return rc;
         const int64_t total = n_slots * k;
         pack_tile_coeffs_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(
-            coeffs, ld_c, k, pl->d_tslot_src, n_slots, pl->d_scratch);
+            coeffs, ld_c, k, pl->d_tslot_src, n_slots, img->ptr);
         MPX_CUDA(cudaGetLastError());
     }
-    if (P == 0) return MPX_OK;
+    if (P == 0) return coeffs ? mpx_image_release(img, stream) : MPX_OK;
     TmmaParams prm;
     prm.xx = xx; prm.ld_xx = ld_xx; prm.P = P; prm.out = out; prm.ld_out = ld_out;
-    prm.desc = pl->d_tdesc; prm.coef = pl->d_scratch; prm.gp = pl->d_gp;
+    prm.desc = pl->d_tdesc; prm.coef = img->ptr; prm.gp = pl->d_gp;
     prm.n_chunks = pl->tprog.n_chunks; prm.m = pl->m; prm.gp_rows = pl->gp_rows;
     for (int i = 0; i < 8; ++i) prm.max_exp[i] = i < pl->m ? pl->max_exp[i] : 0;
     const int ks = pl->tprog.ks_max;
+#ifdef MPX_TUNING
     static const int env_mt = getenv("MPX_TMMA_MT") ? atoi(getenv("MPX_TMMA_MT")) : 0;   // experiment knob
+#else
+    constexpr int env_mt = 0;
+#endif
     const bool mt2 = env_mt ? env_mt == 2 : ks > 5;
     const size_t smem = tmma_smem_bytes(pl, mt2 ? 128 : 256);
     if (mt2) {
-        if (ks <= 3) return launch_tmma<3, 8, 2, 3>(prm, k, smem, stream);
-        if (ks <= 5) return launch_tmma<5, 8, 2, 3>(prm, k, smem, stream);
-        if (ks <= 9) return launch_tmma<9, 8, 2, 2>(prm, k, smem, stream);
-        if (ks <= 17) return launch_tmma<17, 8, 2, 1>(prm, k, smem, stream);
+        if (ks <= 3) return tmma_done(launch_tmma<3, 8, 2, 3>(prm, k, smem, stream), img, stream);
+        if (ks <= 5) return tmma_done(launch_tmma<5, 8, 2, 3>(prm, k, smem, stream), img, stream);
+        if (ks <= 9) return tmma_done(launch_tmma<9, 8, 2, 2>(prm, k, smem, stream), img, stream);
+        if (ks <= 17) return tmma_done(launch_tmma<17, 8, 2, 1>(prm, k, smem, stream), img, stream);
     } else {
-        if (ks <= 3) return launch_tmma<3, 8, 4, 2>(prm, k, smem, stream);
-        if (ks <= 5) return launch_tmma<5, 8, 4, 2>(prm, k, smem, stream);
-        if (ks <= 9) return launch_tmma<9, 8, 4, 1>(prm, k, smem, stream);
-        if (ks <= 17) return launch_tmma<17, 8, 4, 1>(prm, k, smem, stream);
+        if (ks <= 3) return tmma_done(launch_tmma<3, 8, 4, 2>(prm, k, smem, stream), img, stream);
+        if (ks <= 5) return tmma_done(launch_tmma<5, 8, 4, 2>(prm, k, smem, stream), img, stream);
+        if (ks <= 9) return tmma_done(launch_tmma<9, 8, 4, 1>(prm, k, smem, stream), img, stream);
+        if (ks <= 17) return tmma_done(launch_tmma<17, 8, 4, 1>(prm, k, smem, stream), img, stream);
     }
     return mpx_fail(MPX_ERR_UNSUPPORTED, "dimension-0 table too long for the tensor-core tree kernel");
 }

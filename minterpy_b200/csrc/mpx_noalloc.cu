@@ -41,6 +41,16 @@ int noalloc_image(int device, double **ptr_out)
     if (!g_image_ptr[device]) {
         double *p = nullptr;
         cudaError_t e = cudaGetSymbolAddress((void **)&p, g_noalloc_image);
+        if (e == cudaErrorMemoryAllocation) {
+            // with lazy module loading (the runtime's default) the device image that holds the
+            // array is only placed on the GPU now; if the application has already taken all
+            // device memory for its own pool there is no room left for it
+            cudaGetLastError();
+            return mpx_fail(MPX_ERR_NOMEM,
+                            "mpx_eval_noalloc set-up: no device memory left for the library's 8 MiB "
+                            "scratch array; make the first call on each device before the application "
+                            "takes its memory pool, or run with CUDA_MODULE_LOADING=EAGER");
+        }
         if (e != cudaSuccess || p == nullptr)
             return mpx_fail(MPX_ERR_CUDA, std::string("cudaGetSymbolAddress(no-alloc scratch): ") +
                                               cudaGetErrorString(e));
@@ -73,15 +83,13 @@ extern "C" int mpx_eval_noalloc(mpx_plan *pl, const double *xx, int64_t P, int64
     int rc = noalloc_image(pl->device, &image);     // first call on this device: set-up
     if (rc != MPX_OK) return rc;
 
-    // Run the regular launch sequence with the fixed array standing in for the plan's scratch.
-    // Its capacity check passes (need <= MPX_NOALLOC_BYTES), so nothing is allocated or freed.
-    std::lock_guard<std::mutex> lock(pl->mu);
-    double *saved_ptr = pl->d_scratch;
-    const size_t saved_bytes = pl->scratch_bytes;
-    pl->d_scratch = image;
-    pl->scratch_bytes = MPX_NOALLOC_BYTES;
-    rc = mpx_launch_eval(pl, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, (cudaStream_t)stream);
-    pl->d_scratch = saved_ptr;
-    pl->scratch_bytes = saved_bytes;
-    return rc;
+    // The regular launch sequence, with the fixed array as the image that receives the packed
+    // coefficients.  It is marked fixed: it is never grown or freed, and it carries no event
+    // (creating one would be an allocating call) -- overlapping calls are the caller's to avoid.
+    MpxImage fixed_image;
+    fixed_image.ptr = image;
+    fixed_image.bytes = MPX_NOALLOC_BYTES;
+    fixed_image.fixed = true;
+    return mpx_launch_eval(pl, &fixed_image, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out,
+                           (cudaStream_t)stream);
 }

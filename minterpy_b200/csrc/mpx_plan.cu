@@ -22,6 +22,11 @@ int mpx_fail(int code, const std::string &msg)
 extern "C" const char *mpx_last_error(void) { return g_last_error.c_str(); }
 extern "C" int mpx_version(void) { return 100; }
 
+// Test hook (not in the public header), read when a plan is built: 0 = choose by padding
+// overhead, 1 = tensor-core tree kernel whenever it can be built, 2 = never.
+static int mpx_test_tmma = 0;
+extern "C" void mpx_debug_set_tmma(int mode) { mpx_test_tmma = mode; }
+
 namespace {
 
 // lexicographic order with the LAST column most significant (np.lexsort(exponents.T),
@@ -51,6 +56,18 @@ double reciprocal_or_zero(double dv)
     const uint64_t mant = bits & 0xfffffffffffffull;
     const bool ordinary = ex >= 1023 - 200 && ex <= 1023 + 200 && mant != 0xfffffffffffffull;
     return ordinary ? 1.0 / dv : 0.0;      // host division: RN(1/d)
+}
+
+// d = +-2^j (1 - 2^-53) with a moderate exponent: significand all ones.  Returns +-2^j in *pw.
+bool all_ones_divisor(double dv, double *pw)
+{
+    uint64_t bits;
+    std::memcpy(&bits, &dv, 8);
+    const int ex = (int)((bits >> 52) & 0x7ff);
+    const uint64_t mant = bits & 0xfffffffffffffull;
+    if (mant != 0xfffffffffffffull || ex < 1023 - 200 || ex > 1023 + 200) return false;
+    *pw = std::ldexp(dv < 0 ? -1.0 : 1.0, ex - 1023 + 1);
+    return true;
 }
 
 int64_t find_sorted(const int64_t *e, const std::vector<int64_t> &order, int m,
@@ -348,7 +365,11 @@ void slice_rows_of_group(const int64_t *e, int64_t N, int m, int lo, int hi,
     slice_off.push_back((int32_t)N);
     // Small slices are merged with their successors (they stay independent, they just share a
     // CTA): a CTA should own a few hundred rows so that all its warps find fibers to work on.
+#ifdef MPX_TUNING
     static const int merge_rows = getenv("MPX_DDS_MERGE_ROWS") ? atoi(getenv("MPX_DDS_MERGE_ROWS")) : MPX_DDS_MERGE_ROWS;
+#else
+    constexpr int merge_rows = MPX_DDS_MERGE_ROWS;
+#endif
     std::vector<int32_t> merged_off;
     int32_t begin = 0;
     for (size_t t = 0; t + 1 < slice_off.size(); ++t) {
@@ -519,17 +540,17 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
         rc = compile_program(e, N, m, order, mpx_l0p_for(pl->max_exp[0]), pl->prog, err);
         if (rc != MPX_OK) return mpx_fail(rc, err);
     }
-    if (complete && m >= 2 && m <= 8 && pl->max_exp[0] + 1 <= 68 && !getenv("MPX_NO_TMMA")) {
+    if (complete && m >= 2 && m <= 8 && pl->max_exp[0] + 1 <= 68 && mpx_test_tmma != 2) {
         compile_tile_program(e, N, m, pl->tprog);
         // Worth it only for long dimension-0 tables (more than 5 k-steps, n > 19) whose tiles
         // carry almost no zero padding -- in practice full tensor grids (lp = inf).  Measured
         // on the B200: cfg5 (9 % more FMAs than the DFMA tree kernel) 1.18e13 vs 9.9e12 pm/s;
         // m=3, n=24, lp=2 (about 25 % more) 5.5e12 vs 9.6e12; cfg2 (about 40 % more, short
-        // tiles) 6.8e12 vs 9.3e12.  MPX_FORCE_TMMA=1 takes it whenever it was built (tests,
-        // experiments).
+        // tiles) 6.8e12 vs 9.3e12.  The test hook mpx_debug_set_tmma(1) takes it whenever it was
+        // built, (2) never builds it.
         // (the threshold was tuned on FMA counts that included one more per leaf)
         const int64_t tree_fma = pl->tree_ok ? pl->prog.fma_per_point + pl->prog.n_leaves : 0;
-        pl->tprog.usable = getenv("MPX_FORCE_TMMA") != nullptr || !pl->tree_ok ||
+        pl->tprog.usable = mpx_test_tmma == 1 || !pl->tree_ok ||
                            (pl->tprog.ks_max > 5 && 100 * pl->tprog.fma_per_point <= 110 * tree_fma);
     }
     // upper-level exponents of the first leaf (0 for every downward-closed set)
@@ -629,6 +650,36 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
                             dy[2 * ((size_t)l * max_len + r) + 1] = reciprocal_or_zero(dv);
                         }
                 }
+                if (max_len <= 40) {
+                    std::vector<double> dy2v(dy);
+                    std::vector<unsigned long long> fmask(max_len, 0ull);
+                    dd.cols_ok = true;
+                    for (int l = 0; l < max_len; ++l)
+                        for (int r = l + 1; r < max_len; ++r) {
+                            const size_t at = 2 * ((size_t)l * max_len + r);
+                            if (dy[at + 1] != 0.0) continue;             // ordinary divisor
+                            double pw = 0.0;
+                            if (!all_ones_divisor(dy[at], &pw)) { dd.cols_ok = false; continue; }
+                            dy2v[at] = pw;                               // +-2^j
+                            dy2v[at + 1] = 1.0 / pw;                     // +-2^-j, exact
+                            fmask[l] |= 1ull << r;
+                        }
+                    if (dd.cols_ok) {
+                        if ((rc = upload(&dd.d_dy2, dy2v)) != MPX_OK) return rc;
+                        if ((rc = upload(&dd.d_fmask, fmask)) != MPX_OK) return rc;
+                    }
+                }
+                if (max_len <= MPX_DDS_REG_LEN) {
+                    dd.h_pairs.assign((size_t)MPX_DDS_REG_LEN * (MPX_DDS_REG_LEN - 1), 1.0);
+                    dd.all_fast = true;
+                    for (int r = 1; r < max_len; ++r)
+                        for (int l = 0; l < r; ++l) {
+                            const size_t at = 2 * ((size_t)r * (r - 1) / 2 + l);
+                            dd.h_pairs[at] = dy[2 * ((size_t)l * max_len + r)];
+                            dd.h_pairs[at + 1] = dy[2 * ((size_t)l * max_len + r) + 1];
+                            dd.all_fast = dd.all_fast && dd.h_pairs[at + 1] != 0.0;
+                        }
+                }
                 if ((rc = upload(&dd.d_woff, woff)) != MPX_OK) return rc;
                 if ((rc = upload(&dd.d_wrows, wrows)) != MPX_OK) return rc;
                 if ((rc = upload(&dd.d_dy, dy)) != MPX_OK) return rc;
@@ -656,13 +707,19 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
     cudaFree(pl->d_exp8);
     cudaFree(pl->d_max_exp);
     cudaFree(pl->d_exp64);
-    cudaFree(pl->d_scratch);
+    mpx_image_destroy(&pl->image);
+    mpx_image_destroy(&pl->host_image);
     for (int b = 0; b < 2; ++b) {
         cudaFree(pl->h_x[b]);
         cudaFree(pl->h_o[b]);
+        if (pl->p_x[b]) cudaFreeHost(pl->p_x[b]);
+        if (pl->p_o[b]) cudaFreeHost(pl->p_o[b]);
         if (pl->h_stream[b]) cudaStreamDestroy(pl->h_stream[b]);
+        if (pl->h_done[b]) cudaEventDestroy(pl->h_done[b]);
+        if (pl->h_up[b]) cudaEventDestroy(pl->h_up[b]);
     }
     cudaFree(pl->h_c);
+    cudaFree(pl->h_v);
     if (pl->h_event) cudaEventDestroy(pl->h_event);
     for (DdsGroup &g : pl->dds_groups) {
         cudaFree(g.d_slice_off);
@@ -683,6 +740,8 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
         cudaFree(dd.d_woff);
         cudaFree(dd.d_wrows);
         cudaFree(dd.d_dy);
+        cudaFree(dd.d_dy2);
+        cudaFree(dd.d_fmask);
         cudaFree(dd.d_gcol);
     }
     delete pl;
@@ -700,7 +759,7 @@ extern "C" int mpx_plan_info(const mpx_plan *pl, int what, int64_t *value_out)
     case MPX_INFO_DDS_UPDATES: *value_out = pl->dds_updates; break;
     case MPX_INFO_LEAVES: *value_out = pl->prog.n_leaves; break;
     case MPX_INFO_DEVICE: *value_out = pl->device; break;
-    case MPX_INFO_SCRATCH_BYTES: *value_out = (int64_t)pl->scratch_bytes; break;
+    case MPX_INFO_SCRATCH_BYTES: *value_out = (int64_t)pl->image.bytes; break;
     case MPX_INFO_CHUNKS: *value_out = pl->prog.n_chunks; break;
     case MPX_INFO_SMALLK_KERNEL:
         *value_out = mpx_tmma_eligible(pl, 1) ? 1 : (pl->tree_ok ? 0 : 2);
@@ -714,16 +773,48 @@ extern "C" int mpx_plan_info(const mpx_plan *pl, int what, int64_t *value_out)
     return MPX_OK;
 }
 
-int mpx_ensure_scratch(mpx_plan *pl, size_t bytes)
+int mpx_image_acquire(MpxImage *img, size_t bytes, cudaStream_t stream)
 {
-    if (bytes <= pl->scratch_bytes) return MPX_OK;
-    if (pl->d_scratch) MPX_CUDA(cudaFree(pl->d_scratch));
-    pl->d_scratch = nullptr;
-    pl->scratch_bytes = 0;
-    size_t want = std::max(bytes, (size_t)1 << 20);
-    MPX_CUDA(cudaMalloc((void **)&pl->d_scratch, want));
-    pl->scratch_bytes = want;
+    if (bytes > img->bytes) {
+        if (img->fixed)
+            return mpx_fail(MPX_ERR_UNSUPPORTED, "packed coefficients exceed the fixed scratch array");
+        // cudaFree waits for all work on the device, readers of the old image included
+        if (img->ptr) MPX_CUDA(cudaFree(img->ptr));
+        img->ptr = nullptr;
+        img->bytes = 0;
+        img->in_use = false;
+        const size_t want = std::max(bytes, (size_t)1 << 20);
+        MPX_CUDA(cudaMalloc((void **)&img->ptr, want));
+        img->bytes = want;
+    }
+    if (img->in_use && img->last_stream != stream) {
+        // a capturing stream must not wait on an event from outside its graph; such callers
+        // order their streams themselves (as the header asks)
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        MPX_CUDA(cudaStreamIsCapturing(stream, &cap));
+        if (cap == cudaStreamCaptureStatusNone) MPX_CUDA(cudaStreamWaitEvent(stream, img->busy, 0));
+    }
     return MPX_OK;
+}
+
+int mpx_image_release(MpxImage *img, cudaStream_t stream)
+{
+    if (img->fixed) return MPX_OK;      // fixed images: the caller serialises (documented)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    MPX_CUDA(cudaStreamIsCapturing(stream, &cap));
+    if (cap != cudaStreamCaptureStatusNone) return MPX_OK;
+    if (!img->busy) MPX_CUDA(cudaEventCreateWithFlags(&img->busy, cudaEventDisableTiming));
+    MPX_CUDA(cudaEventRecord(img->busy, stream));
+    img->last_stream = stream;
+    img->in_use = true;
+    return MPX_OK;
+}
+
+void mpx_image_destroy(MpxImage *img)
+{
+    if (!img->fixed) cudaFree(img->ptr);
+    if (img->busy) cudaEventDestroy(img->busy);
+    *img = MpxImage();
 }
 
 // Host-only view of the compiled evaluation program, for tests of the index-set compiler

@@ -57,6 +57,13 @@ class Plan:
                                         gp.ctypes.data, gp.shape[0], ctypes.byref(handle))
         _lib.check(rc)
         self._h = handle
+        # private copies: the cache compares them with the caller's arrays on every hit
+        self.exponents = e.copy()
+        self.generating_points = gp.copy()
+
+    def same_space(self, e, gp):
+        return (self.exponents.shape == e.shape and self.generating_points.shape == gp.shape and
+                np.array_equal(self.exponents, e) and np.array_equal(self.generating_points, gp))
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -179,14 +186,18 @@ def get_plan(exponents, generating_points, device=None):
     gp = np.ascontiguousarray(generating_points, dtype=np.float64)
     if device is None:
         device = _current_device()
-    # content key: two independent 32-bit checksums per array, computed without copying
+    # The key is only a hash (two 32-bit checksums per array, computed without copying); a hit
+    # is confirmed by comparing the arrays with the plan's own copies, so a checksum collision
+    # costs a rebuild, never a wrong plan.
     key = (int(device), e.shape, gp.shape, zlib.crc32(e), zlib.adler32(e), zlib.crc32(gp),
            zlib.adler32(gp))
     with _cache_lock:
         plan = _cache.get(key)
+        if plan is not None and not plan.same_space(e, gp):
+            plan = None
         if plan is None:
             plan = Plan(e, gp, device)
-            if len(_cache) >= _CACHE_MAX:
+            if key not in _cache and len(_cache) >= _CACHE_MAX:
                 _cache.pop(next(iter(_cache)))
             _cache[key] = plan
     return plan

@@ -364,12 +364,19 @@ def test_long_higher_dimensions(mpb):
         assert rel_err(got, oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL
 
 
-@pytest.mark.parametrize("force", ["MPX_FORCE_TMMA", "MPX_NO_TMMA"])
-def test_both_tree_kernels(mpb, golden_small, golden_cfg, monkeypatch, force):
+@pytest.fixture()
+def tmma_mode():
+    from minterpy_b200 import _lib
+    yield _lib.lib().mpx_debug_set_tmma
+    _lib.lib().mpx_debug_set_tmma(0)
+
+
+@pytest.mark.parametrize("force", [1, 2])
+def test_both_tree_kernels(mpb, golden_small, golden_cfg, tmma_mode, force):
     """Complete index sets with few polynomials can run on the DFMA tree kernel (mpx_eval.cu) or
     on the tensor-core tree kernel (mpx_eval_tmma.cu); the plan picks by padding overhead.  Both
-    are forced here (the variable is read when the plan is built) on every golden shape."""
-    monkeypatch.setenv(force, "1")
+    are forced here (test hook, read when the plan is built) on every golden shape."""
+    tmma_mode(force)
     for tag in SMALL_TAGS:
         e, gp, xx = golden_small[f"{tag}/exponents"], golden_small[f"{tag}/generating_points"], golden_small[f"{tag}/xx"]
         plan = mpb.Plan(e, gp)
@@ -467,38 +474,29 @@ def test_concurrent_host_threads(mpb, golden_cfg):
         assert np.array_equal(we, ge) and np.array_equal(wd, gd) and np.array_equal(wm, gm)
 
 
-def test_dds_fused_slice_kernel_still_bit_exact():
+def test_dds_fused_slice_kernel_still_bit_exact(mpb, golden_small, golden_cfg):
     """The default dds path is one warp per fiber; the fused slice kernel stays as the fallback
-    for fibers whose buffers do not fit shared memory (MPX_DDS_MODE=group selects it, read once
-    per process -- hence a child process).  Same goldens, same bit-exact bar."""
-    import os
-    import subprocess
-    import sys
-    code = r'''
-import sys
-sys.path.insert(0, "tests"); sys.path.insert(0, "tests/golden")
-import numpy as np, golden_io, minterpy_b200 as mpb
-small = golden_io.load("small")
-n = 0
-for tag in sorted({k.split("/")[0] for k in small}):
-    plan = mpb.get_plan(small[f"{tag}/exponents"], small[f"{tag}/generating_points"])
-    for k in (1, 10):
-        assert np.array_equal(plan.dds(small[f"{tag}/k{k}/dds_in"]), small[f"{tag}/k{k}/dds_ref"]), tag
-        n += 1
-for tag in ("cfg2", "cfg3", "cfg4", "cfg5"):
-    g = golden_io.load(tag)
-    e, gp = g["exponents"], g["generating_points"]
-    vals = golden_io.seeded(g, "dds_seed", "dds_in_sha", g["dds_ref"].shape)
-    assert np.array_equal(mpb.get_plan(e, gp).dds(vals), g["dds_ref"]), tag
-    n += 1
-print("OK", n)
-'''
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, MPX_DDS_MODE="group")
-    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True,
-                         text=True, timeout=600)
-    assert out.returncode == 0, out.stderr[-2000:]
-    assert out.stdout.strip().startswith("OK 76")
+    for fibers whose buffers do not fit shared memory (a test hook routes every call through
+    it).  Same goldens, same bit-exact bar."""
+    from minterpy_b200 import _lib
+    _lib.lib().mpx_debug_set_dds_group(1)
+    try:
+        n = 0
+        for tag in SMALL_TAGS:
+            plan = mpb.get_plan(golden_small[f"{tag}/exponents"], golden_small[f"{tag}/generating_points"])
+            for k in (1, 10):
+                assert np.array_equal(plan.dds(golden_small[f"{tag}/k{k}/dds_in"]),
+                                      golden_small[f"{tag}/k{k}/dds_ref"]), tag
+                n += 1
+        for tag in ("cfg2", "cfg3", "cfg4", "cfg5"):
+            g = golden_cfg(tag)
+            e, gp = g["exponents"], g["generating_points"]
+            vals = golden_io.seeded(g, "dds_seed", "dds_in_sha", g["dds_ref"].shape)
+            assert np.array_equal(mpb.get_plan(e, gp).dds(vals), g["dds_ref"]), tag
+            n += 1
+        assert n == 76
+    finally:
+        _lib.lib().mpx_debug_set_dds_group(0)
 
 
 def test_one_thread_per_gpu(mpb, golden_cfg):

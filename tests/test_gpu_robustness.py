@@ -1,0 +1,247 @@
+"""GPU tests of the host-side machinery around the kernels: coefficient images shared between
+the tensor path and the NumPy path of one plan, streams, pageable host memory, the
+bulk-copy ring of the tree kernel under stress, the plan cache.  All through the C ABI."""
+import ctypes
+import threading
+
+import numpy as np
+import pytest
+
+import golden_io
+import oracle
+
+pytestmark = pytest.mark.gpu
+EVAL_RTOL = 1e-13
+
+
+def rel_err(got, ref):
+    return float(np.max(np.abs(np.asarray(got) - np.asarray(ref))) / max(np.max(np.abs(ref)), 1e-300))
+
+
+@pytest.fixture(scope="module")
+def mpb():
+    import torch
+    assert torch.cuda.is_available(), "the gpu tests need a CUDA device"
+    import minterpy_b200
+    return minterpy_b200
+
+
+def test_tensor_call_keeps_its_coefficients_while_a_numpy_call_repacks(mpb, golden_cfg):
+    """A long tensor-path evaluation is still running when a NumPy-path evaluation with other
+    coefficients enters the same plan (plans are shared by content, so callers cannot know).
+    Each path packs into an image of its own; both results must be right."""
+    import torch
+    g = golden_cfg("cfg2")
+    e, gp = g["exponents"], g["generating_points"]
+    N, m = e.shape
+    plan = mpb.get_plan(e, gp)
+    rng = np.random.default_rng(5)
+    P = 3_000_000                                    # ~8 ms of kernel: the call returns long before
+    xx = torch.rand((P, m), dtype=torch.float64, device="cuda") * 2 - 1
+    c_t = torch.as_tensor(rng.uniform(-1, 1, (N, 1)), device="cuda")
+    c_n = rng.uniform(-1, 1, (N, 1)) * 100.0
+    xn = rng.uniform(-1, 1, (20_000, m))
+    idx = torch.randint(0, P, (32,), device="cuda")
+    for _ in range(3):
+        y_t = plan.eval(xx, c_t)                     # enqueued, still running
+        y_n = plan.eval(xn, c_n)                     # NumPy path: uploads + packs + evaluates
+        torch.cuda.synchronize()
+        ref_t = oracle.eval_newton_polynomials(xx[idx].cpu().numpy(), c_t.cpu().numpy(), e, gp, nthreads=4)
+        assert rel_err(y_t[idx].cpu().numpy(), ref_t) <= EVAL_RTOL
+        assert rel_err(y_t[-4:].cpu().numpy(),
+                       oracle.eval_newton_polynomials(xx[-4:].cpu().numpy(), c_t.cpu().numpy(), e, gp)) <= EVAL_RTOL
+        assert rel_err(y_n[:64], oracle.eval_newton_polynomials(xn[:64], c_n, e, gp)) <= EVAL_RTOL
+
+
+def test_two_streams_on_one_plan(mpb, golden_cfg):
+    """Two torch streams evaluate different polynomials on one plan back to back: the second
+    call's repack waits (on the device) for the first call's kernel."""
+    import torch
+    g = golden_cfg("cfg2")
+    e, gp = g["exponents"], g["generating_points"]
+    N, m = e.shape
+    plan = mpb.get_plan(e, gp)
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    xx = torch.rand((2_000_000, m), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+    ca = torch.rand((N, 1), generator=gen, dtype=torch.float64, device="cuda")
+    cb = -7.0 * torch.rand((N, 1), generator=gen, dtype=torch.float64, device="cuda")
+    want_a, want_b = plan.eval(xx, ca), plan.eval(xx, cb)
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    for _ in range(4):
+        with torch.cuda.stream(s1):
+            ya = plan.eval(xx, ca)
+        with torch.cuda.stream(s2):
+            yb = plan.eval(xx, cb)
+        torch.cuda.synchronize()
+        assert torch.equal(ya, want_a) and torch.equal(yb, want_b)
+
+
+def test_threads_mixing_tensor_and_numpy_calls(mpb, golden_cfg):
+    import torch
+    g = golden_cfg("cfg5")
+    e, gp = g["exponents"], g["generating_points"]
+    N, m = e.shape
+    plan = mpb.get_plan(e, gp)
+    rng = np.random.default_rng(9)
+    xs = [rng.uniform(-1, 1, (40_000 + 1000 * i, m)) for i in range(4)]
+    cs = [rng.uniform(-1, 1, (N, 1 + i % 2)) * (i + 1) for i in range(4)]
+    want = [plan.eval(x, c) for x, c in zip(xs, cs)]
+    got, errors = [None] * 4, []
+
+    def work(i):
+        try:
+            for _ in range(5):
+                if i % 2:
+                    got[i] = plan.eval(xs[i], cs[i])
+                else:
+                    st = torch.cuda.Stream()
+                    with torch.cuda.stream(st):
+                        y = plan.eval(torch.as_tensor(xs[i], device="cuda"), torch.as_tensor(cs[i], device="cuda"))
+                    st.synchronize()
+                    got[i] = y.cpu().numpy()
+        except Exception as ex:       # noqa: BLE001
+            errors.append(ex)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errors, errors
+    for w, g_ in zip(want, got):
+        assert np.array_equal(w, g_)
+
+
+def _host_call(plan, xx, c, out):
+    from minterpy_b200 import _lib
+    rc = _lib.lib().mpx_eval_host(plan._h, xx.ctypes.data, xx.shape[0], xx.strides[0] // 8,
+                                  c.ctypes.data, c.shape[1], c.strides[0] // 8, out.ctypes.data,
+                                  out.strides[0] // 8)
+    _lib.check(rc)
+
+
+def test_pageable_and_page_locked_host_buffers_agree(mpb, golden_cfg):
+    """mpx_eval_host / mpx_dds_host stage pageable arrays through page-locked blocks with host
+    threads; page-locked arrays go to the copy engines directly.  Same bits either way, also
+    with padded rows (leading dimensions larger than the row) and several blocks."""
+    import torch
+    from minterpy_b200 import _lib
+    g = golden_cfg("cfg2")
+    e, gp = g["exponents"], g["generating_points"]
+    N, m = e.shape
+    plan = mpb.get_plan(e, gp)
+    rng = np.random.default_rng(11)
+    P = 4_000_001                                    # 3 blocks of ~1.67e6 points
+    xx = rng.uniform(-1, 1, (P, m + 1))[:, :m]       # pageable, ld = m + 1
+    c = rng.uniform(-1, 1, (N, 1))
+    out_pageable = np.full((P, 2), np.nan)[:, :1]    # pageable, ld = 2
+    _host_call(plan, xx, c, out_pageable)
+    xp = torch.empty((P, m), dtype=torch.float64, pin_memory=True).numpy()
+    xp[:] = xx
+    out_pinned = torch.empty((P, 1), dtype=torch.float64, pin_memory=True).numpy()
+    _host_call(plan, xp, c, out_pinned)
+    assert np.array_equal(out_pageable, out_pinned)
+    idx = rng.integers(0, P, 24)
+    assert rel_err(out_pinned[idx], oracle.eval_newton_polynomials(np.ascontiguousarray(xx[idx]), c, e, gp)) <= EVAL_RTOL
+    # dds: pageable in/out (column blocks repacked by host threads) vs page-locked vs the
+    # reference's result (sha256 of the 59 711 x 256 golden case)
+    g4 = golden_cfg("cfg4")
+    plan4 = mpb.get_plan(g4["exponents"], g4["generating_points"])
+    vals = golden_io.seeded(g4, "dds_wide_seed", "dds_wide_in_sha", (g4["exponents"].shape[0], 256))
+    lib = _lib.lib()
+    out_a = np.empty_like(vals)
+    _lib.check(lib.mpx_dds_host(plan4._h, vals.ctypes.data, vals.shape[1], vals.shape[1],
+                                out_a.ctypes.data, vals.shape[1]))
+    vp = torch.empty(vals.shape, dtype=torch.float64, pin_memory=True).numpy()
+    vp[:] = vals
+    out_b = torch.empty(vals.shape, dtype=torch.float64, pin_memory=True).numpy()
+    _lib.check(lib.mpx_dds_host(plan4._h, vp.ctypes.data, vals.shape[1], vals.shape[1],
+                                out_b.ctypes.data, vals.shape[1]))
+    assert golden_io.sha256_of(out_a) == str(g4["dds_wide_ref_sha"])
+    assert np.array_equal(out_a, out_b)
+    k = 100                                          # ragged column blocks, padded rows
+    wide_in = np.full((vals.shape[0], k + 3), np.nan)
+    wide_in[:, :k] = vals[:, :k]
+    wide_out = np.full((vals.shape[0], k + 5), np.nan)
+    _lib.check(lib.mpx_dds_host(plan4._h, wide_in.ctypes.data, k, k + 3, wide_out.ctypes.data, k + 5))
+    assert np.array_equal(wide_out[:, :k], out_a[:, :k]) and np.isnan(wide_out[:, k:]).all()
+
+
+@pytest.mark.parametrize("stages", [2, 3, 4])
+def test_tree_kernel_ring_under_stress(mpb, golden_cfg, stages):
+    """The tree kernel streams its program through a shared-memory ring refilled by thread 0
+    (cp.async.bulk + mbarrier, csrc/mpx_eval.cu).  Many chunks through few stages, point counts
+    that leave tail CTAs and odd CTA counts, several polynomials per launch: every value is
+    checked against the default configuration and a sample against the oracle."""
+    import torch
+    from minterpy_b200 import _lib
+    lib = _lib.lib()
+    for tag in ("cfg4", "cfg2", "cfg3"):             # 60+, 26 and ~20 chunks
+        g = golden_cfg(tag)
+        e, gp = g["exponents"], g["generating_points"]
+        N, m = e.shape
+        plan = mpb.Plan(e, gp)
+        assert plan.info(_lib.INFO_CHUNKS) > 2 * stages
+        gen = torch.Generator(device="cuda").manual_seed(17 + stages)
+        for P, k in ((1, 1), (1023, 2), (151_553, 1), (37 * 1024 + 5, 3)):
+            xx = torch.rand((P, m), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+            c = torch.rand((N, k), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+            want = plan.eval(xx, c)
+            torch.cuda.synchronize()
+            lib.mpx_debug_set_eval_stages(stages)
+            try:
+                for _ in range(3):
+                    got = plan.eval(xx, c)
+                    torch.cuda.synchronize()
+                    # different ring depth = different CTA shape, same arithmetic per point
+                    assert torch.equal(got, want), (tag, P, k)
+            finally:
+                lib.mpx_debug_set_eval_stages(0)
+            sel = torch.randint(0, P, (min(P, 8),), generator=gen, device="cuda")
+            ref = oracle.eval_newton_polynomials(xx[sel].cpu().numpy(), c.cpu().numpy(), e, gp, nthreads=4)
+            assert rel_err(want[sel].cpu().numpy(), ref) <= EVAL_RTOL
+
+
+def test_plan_cache_confirms_the_arrays(mpb, golden_small, monkeypatch):
+    """A cache hit is confirmed by comparing the arrays: with every checksum forced to collide,
+    two different index sets still get their own plans."""
+    import zlib
+    from minterpy_b200 import plan as plan_mod
+    plan_mod.clear_plan_cache()
+    monkeypatch.setattr(zlib, "crc32", lambda a: 1)
+    monkeypatch.setattr(zlib, "adler32", lambda a: 2)
+    ta, tb = "m2_n4_lp1.0", "m2_n4_lpinf"
+    ea, gpa = golden_small[f"{ta}/exponents"], golden_small[f"{ta}/generating_points"]
+    eb = ea.copy()
+    eb[-1, 0] += 1                                   # same shape, different set
+    pa = plan_mod.get_plan(ea, gpa)
+    pb = plan_mod.get_plan(eb, gpa)
+    assert pa is not pb and np.array_equal(pb.exponents, eb)
+    assert plan_mod.get_plan(eb, gpa) is pb
+    xx, c = golden_small[f"{ta}/xx"], golden_small[f"{ta}/k1/coeffs"]
+    assert rel_err(pb.eval(xx, c), oracle.eval_newton_polynomials(xx, c, eb, gpa)) <= EVAL_RTOL
+    plan_mod.clear_plan_cache()
+
+
+def test_regression_on_a_set_with_holes_with_tensors(mpb, nxt_rows):
+    """Lagrange-basis regression on an incomplete index set, tensor inputs: the Lagrange->Newton
+    operator is the dense MatrixOperator there and has to hand its matrix over on the device."""
+    import torch
+    from minterpy_b200.regression import compute_regression_matrix
+    nxt = nxt_rows
+    e, gp = nxt["inc/0/exponents"], nxt["inc/0/generating_points"]
+    mi = mpb.MultiIndexSet(e, lp_degree=float(nxt["inc/0/lp"]))
+    grid = mpb.Grid(mi)
+    basis = mpb.LagrangePolynomial(mi, None, grid=grid)
+    rng = np.random.default_rng(2)
+    xx = rng.uniform(-1, 1, (50, e.shape[1]))
+    r_np = compute_regression_matrix(basis, xx)
+    r_t = compute_regression_matrix(basis, torch.as_tensor(xx, device="cuda"))
+    assert r_t.is_cuda and rel_err(r_t.cpu().numpy(), r_np) <= 1e-12
+    # interpolatory on the nodes: the Lagrange basis is the identity there
+    ident = compute_regression_matrix(basis, torch.as_tensor(grid.unisolvent_nodes, device="cuda"))
+    assert np.max(np.abs(ident.cpu().numpy() - np.eye(len(mi)))) <= 1e-10
+
+
+@pytest.fixture(scope="module")
+def nxt_rows():
+    return golden_io.load("next_rows")

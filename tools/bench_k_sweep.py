@@ -2,7 +2,8 @@
 """Evaluation time against the number of polynomials k (device-resident inputs, CUDA events,
 median of 3 after 2 warm-ups): where the tree kernel run once per polynomial and the
 many-polynomial tensor kernel cross.  usage: bench_k_sweep.py <cfgN> <points>;
-MPX_EVAL_MMA_MIN_K=9999 forces the tree kernel, =1 the tensor kernel."""
+MPX_EVAL_MMA_MIN_K=9999 forces the tree kernel, =1 the tensor kernel (the variable is only
+read by a library built with `python -m minterpy_b200.build --tuning`)."""
 import os
 import sys
 

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Evaluation throughput (k = 1, device-resident) of one shape from tests/golden/shapes_extra.npz
 or a BASELINE config, for comparing the two tree kernels:
-   MPX_NO_TMMA=1 / MPX_FORCE_TMMA=1 python tools/bench_shape.py m3_n24_lp2.0 [points]"""
+   python tools/bench_shape.py m3_n24_lp2.0 [points] [tmma: 0 auto | 1 force | 2 never]"""
 import os
 import sys
 
@@ -26,6 +26,8 @@ def main():
         g = golden_io.load("shapes_extra")
         e, gp = g[f"{tag}/exponents"], g[f"{tag}/generating_points"]
     N, m = e.shape
+    if len(sys.argv) > 3:
+        _lib.lib().mpx_debug_set_tmma(int(sys.argv[3]))
     plan = mpb.Plan(e, gp)
     xx = torch.rand((P, m), dtype=torch.float64, device="cuda") * 2 - 1
     c = torch.rand((N, 1), dtype=torch.float64, device="cuda") * 2 - 1

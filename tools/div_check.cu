@@ -59,6 +59,38 @@ __global__ void check(const double *ds, const double *ys, int nd, int iters, uin
     if (bad) atomicAdd(mismatch, bad);
 }
 
+// Second rule (csrc/mpx_dds.cu): for d = s 2^j (1 - 2^-53) -- significand all ones, where the
+// sequence above is NOT exact -- the quotient is the next double after A = a / (s 2^j), away from
+// zero (for a != 0).  Computed exactly as the kernel does: the three instructions with the pair
+// (s 2^j, s 2^-j), then one integer increment of the bit pattern.
+__global__ void check_all_ones(int iters, uint64_t seed, unsigned long long *mismatch, double *example)
+{
+    uint64_t s = seed + (uint64_t)(blockIdx.x * blockDim.x + threadIdx.x) * 0x7654321ull;
+    unsigned long long bad = 0;
+    for (int it = 0; it < iters; ++it) {
+        uint64_t u = splitmix(s);
+        const int j = (int)(splitmix(s) % 401) - 200;                 // 2^j, |j| <= 200
+        const double sgn = (u >> 61) & 1 ? -1.0 : 1.0;
+        const double pw = sgn * ldexp(1.0, j);
+        const double d = sgn * (ldexp(1.0, j) - ldexp(1.0, j - 53));  // all-ones significand
+        uint64_t mant = u & 0xfffffffffffffull;
+        if ((it & 7) == 7) mant = 0;                                  // powers of two: the tie case
+        if ((it & 7) == 6) mant = 0xfffffffffffffull;                 // top of the binade
+        if ((it & 7) == 5) mant &= 0xffull;                           // just above a power of two
+        int ex = (int)((u >> 52) % 1401) - 700;                       // 2^-700 .. 2^700
+        double a = __longlong_as_double((long long)(((uint64_t)(1023 + ex) << 52) | mant));
+        if (u >> 63) a = -a;
+        const double ref = __ddiv_rn(a, d);
+        double q = fast_div<1>(a, pw, 1.0 / pw);
+        q = __longlong_as_double(__double_as_longlong(q) + 1);
+        if (__double_as_longlong(ref) != __double_as_longlong(q)) {
+            if (bad == 0 && atomicAdd(mismatch + 1, 1ull) < 4) { example[0] = a; example[1] = d; }
+            ++bad;
+        }
+    }
+    if (bad) atomicAdd(mismatch, bad);
+}
+
 int main()
 {
     // divisors: all pairwise differences of Chebyshev-Lobatto points (any order gives the same
@@ -96,6 +128,16 @@ int main()
         cudaMemcpy(ex, dex, 16, cudaMemcpyDeviceToHost);
         printf("{\"correction_steps\": %d, \"divisors\": %zu, \"samples\": %.3e, \"mismatches\": %llu, \"example_a\": %.17g, \"example_d\": %.17g}\n",
                steps, ds.size(), (double)blocks * threads * iters, m[0], m[0] ? ex[0] : 0.0, m[0] ? ex[1] : 0.0);
+    }
+    {
+        cudaMemset(dm, 0, 16);
+        check_all_ones<<<blocks, threads>>>(iters, 4242, dm, dex);
+        cudaDeviceSynchronize();
+        unsigned long long m[2]; double ex[2];
+        cudaMemcpy(m, dm, 16, cudaMemcpyDeviceToHost);
+        cudaMemcpy(ex, dex, 16, cudaMemcpyDeviceToHost);
+        printf("{\"rule\": \"all-ones significand: next double away from zero\", \"samples\": %.3e, \"mismatches\": %llu, \"example_a\": %.17g, \"example_d\": %.17g}\n",
+               (double)blocks * threads * iters, m[0], m[0] ? ex[0] : 0.0, m[0] ? ex[1] : 0.0);
     }
     return 0;
 }
