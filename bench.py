@@ -450,22 +450,41 @@ def main():
 
         def e2e_one_job(xh, yh):
             """Strong scaling, N > 1: ONE job -- coefficients broadcast from rank 0 over NCCL,
-            every rank uploads and evaluates its shard of the points, the result shards are
-            all-gathered over NVLink, and every rank reads its shard back to the host."""
+            every rank uploads and evaluates its shard of the points (in pieces, the upload of
+            piece i+1 on a copy stream under the evaluation of piece i), the result shards are
+            all-gathered over NVLink while every rank reads its own shard back to the host."""
             times = []
             c1 = coeffs[:, 0] if k == 1 else coeffs
+            pieces = 8
+            cuts = [P * i // pieces for i in range(pieces + 1)]
+            copy_stream, d2h_stream = torch.cuda.Stream(), torch.cuda.Stream()
+            main = torch.cuda.current_stream()
+            y = torch.empty((P, k), dtype=torch.float64, device=dev)
             for it in range(2 + e2e_steps):
                 barrier()
                 t = time.perf_counter()
                 dist.broadcast(coeffs, src=0)
-                xx.copy_(xh, non_blocking=True)
-                y = mpb.eval_newton_polynomials(xx, c1, e, gp)
-                full = mpd.gather_values(y.reshape(P, k), P_job)
-                yh.copy_(y.reshape(P, k), non_blocking=True)
+                ready = []
+                with torch.cuda.stream(copy_stream):
+                    for i in range(pieces):
+                        xx[cuts[i]:cuts[i + 1]].copy_(xh[cuts[i]:cuts[i + 1]], non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(copy_stream)
+                        ready.append(ev)
+                for i in range(pieces):
+                    main.wait_event(ready[i])
+                    y[cuts[i]:cuts[i + 1]] = mpb.eval_newton_polynomials(
+                        xx[cuts[i]:cuts[i + 1]], c1, e, gp).reshape(-1, k)
+                done = torch.cuda.Event()
+                done.record(main)
+                with torch.cuda.stream(d2h_stream):
+                    d2h_stream.wait_event(done)
+                    yh.copy_(y, non_blocking=True)
+                full = mpd.gather_values(y, P_job)
                 torch.cuda.synchronize()
                 dt = time.perf_counter() - t
                 assert full.shape[0] == P_job
-                del full, y
+                del full
                 if it >= 2:
                     times.append(dt * 1e3)
             dt = max_over_ranks(float(np.mean(times)) * 1e-3)
@@ -473,8 +492,9 @@ def main():
                     "h2d_bytes_per_step": int(P * m * 8), "d2h_bytes_per_step": int(P * k * 8),
                     "ms_per_step": dt * 1e3, "step_ms": times,
                     "api": "minterpy_b200.eval_newton_polynomials(torch) + distributed.gather_values",
-                    "includes": "NCCL broadcast of the coefficients, H2D of the point shard, "
-                                "evaluation, all_gather of the result shards, D2H of the shard"}
+                    "includes": "NCCL broadcast of the coefficients, H2D of the point shard "
+                                "(8 pieces, overlapped with the evaluation), evaluation, all_gather "
+                                "of the result shards, D2H of the shard"}
 
         xh = torch.empty((P, m), dtype=torch.float64, pin_memory=True)
         xh.copy_(xx)

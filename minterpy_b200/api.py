@@ -91,16 +91,22 @@ def _as_host_float(a):
 
 
 def eval_newton_polynomials(xx, coefficients, exponents, generating_points,
-                            verify_input=False, batch_size=None):
+                            verify_input=False, batch_size=None, devices=None):
     """Evaluate polynomial(s) in Newton form at the query points ``xx``.
 
     ``batch_size`` is accepted for compatibility; the kernel never builds the
     (points x monomials) matrix, so there is nothing to batch and results do not depend on it.
+    ``devices`` (not in the reference): a list of GPU indices, or ``"all"``, shards the points
+    over those GPUs from this one process (``multi.eval_multi_gpu``); default: the current GPU.
     """
     verify_input = verify_input or DEBUG
     exponents = _as_host_int(exponents)
     generating_points = _as_host_float(generating_points)
     _, coefficients, _, _, _, xx = rectify_eval_input(xx, coefficients, exponents, verify_input)
+    if devices is not None:
+        from .multi import eval_multi_gpu
+        return convert_eval_output(eval_multi_gpu(xx, coefficients, exponents, generating_points,
+                                                  None if devices == "all" else devices))
     plan = get_plan(exponents, generating_points)
     return convert_eval_output(plan.eval(xx, coefficients))
 

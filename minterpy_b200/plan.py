@@ -98,6 +98,22 @@ class Plan:
             _lib.check(rc)
         return out
 
+    def eval_into(self, xx, coeffs, out):
+        """NumPy path with a caller-provided result: xx (P, m), coeffs (N, k), out (P, k), all
+        float64 with unit stride along rows (slices of larger arrays are fine)."""
+        for name, a in (("xx", xx), ("coeffs", coeffs), ("out", out)):
+            if a.dtype != np.float64 or a.ndim != 2 or a.strides[1] != 8:
+                raise ValueError(f"{name} must be a 2-D float64 array with contiguous rows")
+        P, k = xx.shape[0], coeffs.shape[1]
+        if out.shape != (P, k) or xx.shape[1] != self.m or coeffs.shape[0] != self.N:
+            raise ValueError("shape mismatch between points, coefficients and result")
+        if P:
+            rc = _lib.lib().mpx_eval_host(self._h, xx.ctypes.data, P, xx.strides[0] // 8,
+                                          coeffs.ctypes.data, k, coeffs.strides[0] // 8,
+                                          out.ctypes.data, out.strides[0] // 8)
+            _lib.check(rc)
+        return out
+
     def _eval_torch(self, xx, coeffs, out=None):
         import torch
         dev = torch.device("cuda", self.device)
