@@ -156,10 +156,23 @@ int mpx_dds_host(mpx_plan *plan, const double *in_h, int k, int64_t ld_in, doubl
  * Dense operator apply out = T @ c.
  *   replaces: MatrixOperator.__matmul__  src/minterpy/schemes/matrix_operator.py:13-22
  * T (rows x cols, ld_t), c (cols x k, ld_c), out (rows x k, ld_out), all device, float64.
+ * Up to 8 coefficient columns run as FMA dot products, more as one pass over T per 32 columns
+ * on the FP64 tensor cores; T is read once per pass and that read bounds the call.
  */
 int mpx_apply_dense(int device, const double *T, int64_t rows, int64_t cols, int64_t ld_t,
                     const double *c, int k, int64_t ld_c, double *out, int64_t ld_out,
                     void *stream);
+
+/*
+ * The same with flags.  MPX_DENSE_LOWER: T is lower triangular (every Newton<->Lagrange matrix
+ * of a sorted index set is: src/minterpy/transformations/utils.py:35-55 builds it with
+ * triangular=True, and so is its inverse); entries to the right of the diagonal are taken as
+ * zero and mostly not read at all -- about half the bytes and half the time.
+ */
+enum { MPX_DENSE_LOWER = 1 };
+int mpx_apply_dense_ex(int device, const double *T, int64_t rows, int64_t cols, int64_t ld_t,
+                       const double *c, int k, int64_t ld_c, double *out, int64_t ld_out,
+                       int flags, void *stream);
 
 /*
  * Evaluate a partial derivative of k polynomials in Newton form at P points.

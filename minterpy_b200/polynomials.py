@@ -14,6 +14,7 @@ import ctypes
 import numpy as np
 
 from . import api, generators
+from . import _lib
 from ._lib import check, lib
 from .plan import _is_torch, get_plan
 
@@ -364,9 +365,13 @@ class MatrixOperator(_Operator):
     a sorted index set, ``transformations/utils.py:35-55``) lets the kernel skip the zero half."""
 
     def __init__(self, matrix, lower_triangular=False, transformation=None):
+        self.lower_triangular = bool(lower_triangular)
+        if self.lower_triangular:
+            # the kernel skips what lies right of the diagonal: make that part exactly zero, so
+            # that the matrix a caller reads back is the operator that is applied
+            matrix = matrix.tril() if _is_torch(matrix) else np.tril(matrix)
         self._host = None if _is_torch(matrix) else np.ascontiguousarray(matrix, dtype=np.float64)
         self._dev = matrix.contiguous() if _is_torch(matrix) else None
-        self.lower_triangular = bool(lower_triangular)
         self.transformation = transformation
 
     def _on_device(self):
@@ -399,9 +404,10 @@ class MatrixOperator(_Operator):
         c2 = (c.reshape(-1, 1) if c.ndim == 1 else c).contiguous()
         out = torch.empty((T.shape[0], c2.shape[1]), dtype=torch.float64, device=T.device)
         stream = torch.cuda.current_stream(T.device).cuda_stream
-        check(lib().mpx_apply_dense(T.device.index, T.data_ptr(), T.shape[0], T.shape[1], T.stride(0),
-                                    c2.data_ptr(), c2.shape[1], c2.stride(0), out.data_ptr(),
-                                    out.stride(0), stream))
+        flags = _lib.MPX_DENSE_LOWER if self.lower_triangular else 0
+        check(lib().mpx_apply_dense_ex(T.device.index, T.data_ptr(), T.shape[0], T.shape[1],
+                                       T.stride(0), c2.data_ptr(), c2.shape[1], c2.stride(0),
+                                       out.data_ptr(), out.stride(0), flags, stream))
         if c.ndim == 1:
             out = out.reshape(-1)
         return out.cpu().numpy() if as_numpy else out
@@ -419,7 +425,11 @@ class LagrangeToNewton(_Transformation):
             return DDSOperator(self.grid, self)
         import torch
         n2l = NodeEvalOperator(self.grid).full_on_device()
-        return MatrixOperator(torch.linalg.inv(n2l), transformation=self)
+        # the Newton->Lagrange matrix is lower triangular (triangular=True above), hence its
+        # inverse: solve against the identity as a triangular system
+        eye = torch.eye(n2l.shape[0], dtype=torch.float64, device=n2l.device)
+        l2n = torch.linalg.solve_triangular(n2l, eye, upper=False)
+        return MatrixOperator(l2n, lower_triangular=True, transformation=self)
 
 
 class NewtonToLagrange(_Transformation):

@@ -33,3 +33,26 @@ def seeded(d, seed_key, sha_key, shape):
     if sha256_of(a) != str(d[sha_key]):
         raise RuntimeError(f"seeded input {seed_key} does not reproduce (numpy RNG drift)")
     return a
+
+
+def corners(m):
+    return np.array([[1.0 if (i >> d) & 1 else -1.0 for d in range(m)] for i in range(2 ** m)])
+
+
+def wide_case(tag):
+    """The wide golden case of a BASELINE config (make_golden_wide.py): 4096 seeded random
+    points + ALL unisolvent nodes + the 2^m corners, the stored coefficient columns, and the
+    reference's values there.  Returns (points, coefficient columns, eval_ref, n2l_ref or None)."""
+    g, w = load(tag), load("wide")
+    e, gp = g["exponents"], g["generating_points"]
+    N, m = e.shape
+    nodes = np.take_along_axis(gp, e, axis=0)
+    if sha256_of(nodes) != str(g["unisolvent_sha"]):
+        raise RuntimeError("unisolvent nodes do not reproduce")
+    xr = draw_uniform(w[f"{tag}/xx_seed"], (4096, m))
+    if sha256_of(xr) != str(w[f"{tag}/xx_sha"]):
+        raise RuntimeError("seeded points do not reproduce (numpy RNG drift)")
+    xx = np.concatenate([xr, nodes, corners(m)])
+    c = seeded(g, "coeffs_seed", "coeffs_sha", (N, int(g["k_eval"])))
+    cols = w[f"{tag}/columns"]
+    return xx, np.ascontiguousarray(c[:, cols]), w[f"{tag}/eval_ref"], w.get(f"{tag}/n2l_ref")

@@ -300,7 +300,8 @@ def test_lagrange_to_newton_on_sets_with_holes(mpb, nxt):
     n2l = mpb.NewtonToLagrange(newt).transformation_operator
     prod = op @ n2l
     assert isinstance(prod, MatrixOperator)
-    assert np.max(np.abs(prod.array_repr_full - np.eye(len(mi)))) <= 1e-11
+    # (entries of the Lagrange->Newton matrix reach 1e3..1e4 here: 1e-10 is ~1e-14 relative)
+    assert np.max(np.abs(prod.array_repr_full - np.eye(len(mi)))) <= 1e-10
     with pytest.raises(ValueError):
         op @ np.ones(len(mi) + 1)
 

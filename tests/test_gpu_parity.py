@@ -73,6 +73,31 @@ def test_config_dds_golden_bit_exact(mpb, golden_cfg, tag):
     assert np.array_equal(plan.dds(g["smooth_in"].reshape(-1, 1)), g["smooth_dds_ref"])
 
 
+@pytest.mark.parametrize("tag", CFGS)
+def test_config_wide_golden(mpb, tag):
+    """SURVEY.md 8c at full width: 4096 random points + ALL unisolvent nodes + the 2^m corners
+    of every BASELINE config against the unmodified reference's values, and NewtonToLagrange at
+    all nodes (cfg2: 24 809, cfg4: 59 711) against the reference's own transformation."""
+    xx, c, ref, n2l = golden_io.wide_case(tag)
+    g = golden_io.load(tag)
+    e, gp = g["exponents"], g["generating_points"]
+    N = e.shape[0]
+    plan = mpb.get_plan(e, gp)
+    got = plan.eval(xx, c)
+    assert got.shape == ref.shape
+    assert rel_err(got, ref) <= EVAL_RTOL
+    if n2l is not None:
+        mi = mpb.MultiIndexSet(e, lp_degree=2.0)
+        newt = mpb.NewtonPolynomial(mi, np.ascontiguousarray(c[:, 0]), grid=mpb.Grid(mi, gp))
+        lag = mpb.NewtonToLagrange(newt)()
+        assert lag.coeffs.shape == (N,)
+        assert rel_err(lag.coeffs, n2l) <= EVAL_RTOL
+        # and back: divided differences of those values return the coefficients (up to the
+        # conditioning of the round trip with random coefficients, 2.5e-8 at cfg2)
+        back = mpb.LagrangeToNewton(lag)()
+        assert rel_err(back.coeffs, c[:, 0]) <= 1e-6
+
+
 def test_cfg4_wide_dds_hash(mpb, golden_cfg):
     """BASELINE config 4 at full size: 59 711 x 256 values, bit-exact through a sha256."""
     g = golden_cfg("cfg4")
@@ -278,6 +303,61 @@ def test_dense_apply(mpb):
         rc = _lib.lib().mpx_apply_dense(0, view.data_ptr(), 301, cols, 1200, ct.data_ptr(), 3, 3,
                                         out.data_ptr(), 3, None)
         _lib.check(rc)
+        assert rel_err(out.cpu().numpy(), wide[:, first:first + cols] @ c) <= 1e-13
+
+
+def test_dense_apply_many_columns_and_lower_triangular(mpb):
+    """k > 8 runs as one pass over T per 32 columns on the FP64 tensor cores (DMMA, contraction
+    index permuted inside 16-column groups); MPX_DENSE_LOWER skips what lies right of the
+    diagonal.  Odd and even leading dimensions, unaligned views, ragged last spans."""
+    import torch
+    from minterpy_b200 import _lib
+    rng = np.random.default_rng(8)
+    lib = _lib.lib()
+    for rows, cols, k in ((1, 1, 9), (70, 70, 16), (130, 97, 12), (513, 513, 17), (33, 1025, 32),
+                          (515, 700, 40), (1027, 1302, 9), (258, 257, 70), (400, 128, 24)):
+        full = rng.uniform(-1, 1, (rows, cols))
+        c = rng.uniform(-1, 1, (cols, k))
+        ct = torch.from_numpy(c).cuda()
+        for flags, T in ((0, full), (_lib.MPX_DENSE_LOWER, np.tril(full))):
+            Tt = torch.from_numpy(T).cuda()
+            out = torch.full((rows, k), float("nan"), dtype=torch.float64, device="cuda")
+            _lib.check(lib.mpx_apply_dense_ex(0, Tt.data_ptr(), rows, cols, cols, ct.data_ptr(), k, k,
+                                              out.data_ptr(), k, flags, None))
+            assert rel_err(out.cpu().numpy(), T @ c) <= 1e-13, (rows, cols, k, flags)
+    # lower-triangular flag on the few-column (FMA) kernels, odd sizes
+    for n, k in ((1027, 1), (1301, 3), (514, 8), (96, 2)):
+        T = np.tril(rng.uniform(-1, 1, (n, n)))
+        c = rng.uniform(-1, 1, (n, k))
+        Tt, ct = torch.from_numpy(T).cuda(), torch.from_numpy(c).cuda()
+        out = torch.empty((n, k), dtype=torch.float64, device="cuda")
+        _lib.check(lib.mpx_apply_dense_ex(0, Tt.data_ptr(), n, n, n, ct.data_ptr(), k, k,
+                                          out.data_ptr(), k, _lib.MPX_DENSE_LOWER, None))
+        assert rel_err(out.cpu().numpy(), T @ c) <= 1e-13
+    # what lies right of the diagonal is NOT read beyond the CTA's own column block: poison it
+    n, k = 777, 11
+    T = np.tril(rng.uniform(-1, 1, (n, n)))
+    poisoned = T.copy()
+    iu = np.triu_indices(n, 64)
+    poisoned[iu] = np.nan
+    c = rng.uniform(-1, 1, (n, k))
+    Tt, ct = torch.from_numpy(poisoned).cuda(), torch.from_numpy(c).cuda()
+    for kk in (11, 2):
+        out = torch.empty((n, kk), dtype=torch.float64, device="cuda")
+        cc = ct[:, :kk].contiguous()
+        _lib.check(lib.mpx_apply_dense_ex(0, Tt.data_ptr(), n, n, n, cc.data_ptr(), kk, kk,
+                                          out.data_ptr(), kk, _lib.MPX_DENSE_LOWER, None))
+        assert rel_err(out.cpu().numpy(), T @ c[:, :kk]) <= 1e-13
+    # unaligned view with many columns
+    wide = rng.uniform(-1, 1, (301, 1200))
+    Wt = torch.from_numpy(wide).cuda()
+    for first, cols in ((1, 1199), (2, 1001)):
+        c = rng.uniform(-1, 1, (cols, 20))
+        ct = torch.from_numpy(c).cuda()
+        out = torch.empty((301, 20), dtype=torch.float64, device="cuda")
+        view = Wt[:, first:first + cols]
+        _lib.check(lib.mpx_apply_dense(0, view.data_ptr(), 301, cols, 1200, ct.data_ptr(), 20, 20,
+                                       out.data_ptr(), 20, None))
         assert rel_err(out.cpu().numpy(), wide[:, first:first + cols] @ c) <= 1e-13
 
 

@@ -114,3 +114,23 @@ def test_derivative_evaluation_against_reference():
         # order zero is the polynomial itself
         plain = oracle.eval_newton_polynomials(x, c, e, gp)[:, 0]
         assert np.array_equal(oracle.deriv_newt_eval(x, c, e, gp, np.zeros(e.shape[1]))[:, 0], plain)
+
+
+@pytest.mark.parametrize("tag", CFGS)
+def test_config_wide_golden(tag):
+    """4096 random points + all unisolvent nodes + corners per BASELINE config,
+    values from the unmodified reference (tests/golden/make_golden_wide.py).  The oracle checks a
+    spread of them here (every random point for the small sets; the GPU test checks them all)."""
+    xx, c, ref, n2l = golden_io.wide_case(tag)
+    g = golden_io.load(tag)
+    e, gp = g["exponents"], g["generating_points"]
+    N, m = e.shape
+    assert ref.shape == (4096 + N + 2 ** m, c.shape[1])
+    step = max(1, (xx.shape[0] * N * c.shape[1]) // 400_000_000)       # bounded CPU time
+    sel = np.unique(np.concatenate([np.arange(0, xx.shape[0], step), np.arange(xx.shape[0] - 2 ** m, xx.shape[0])]))
+    ev = oracle.eval_newton_polynomials(xx[sel], c, e, gp, nthreads=8)
+    assert rel_err(ev, ref[sel]) <= EVAL_RTOL
+    if n2l is not None:
+        # the reference's NewtonToLagrange (barycentric operator) on the first stored column is
+        # evaluation at the unisolvent nodes, which the same reference evaluated above
+        assert rel_err(ref[4096:4096 + N, 0], n2l) <= 1e-12

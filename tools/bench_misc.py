@@ -76,24 +76,31 @@ def main():
                                        "frac": gbs / hbm, "peak_source": src},
                           "l2": "output (8 B x P x N) larger than L2"}))
         del out
-    for rows, k in ((24809, 1), (24809, 4), (24809, 8), (24809, 16), (24808, 1)) if want("dense") else ():
+    cases = ((24809, 1, 0), (24809, 4, 0), (24809, 8, 0), (24809, 16, 0), (24809, 32, 0), (24808, 1, 0),
+             (24808, 16, 0), (24809, 1, 1), (24809, 16, 1))
+    for rows, k, lower in cases if want("dense") else ():
         T = torch.rand((rows, rows), dtype=torch.float64, device="cuda")
+        if lower:
+            T = T.tril()
         c = torch.rand((rows, k), dtype=torch.float64, device="cuda")
         o = torch.empty((rows, k), dtype=torch.float64, device="cuda")
 
         def run():
-            _lib.check(lib.mpx_apply_dense(0, T.data_ptr(), rows, rows, rows, c.data_ptr(), k, k,
-                                           o.data_ptr(), k, stream))
+            _lib.check(lib.mpx_apply_dense_ex(0, T.data_ptr(), rows, rows, rows, c.data_ptr(), k, k,
+                                              o.data_ptr(), k, lower, stream))
         ms = timed(run, args.iters)
-        gbs = rows * rows * 8 / (ms * 1e-3) / 1e9
-        ref = (T[:64] @ c)
-        err = ((o[:64] - ref).abs().max() / ref.abs().max()).item()
-        print(json.dumps({"bench": "apply_dense", "rows": rows, "k": k, "ms": ms, "rel_err_vs_torch": err,
+        needed = rows * (rows + 1) // 2 * 8 if lower else rows * rows * 8     # bytes that must be read
+        gbs = needed / (ms * 1e-3) / 1e9
+        ref = (T[-64:] @ c)
+        err = ((o[-64:] - ref).abs().max() / ref.abs().max()).item()
+        print(json.dumps({"bench": "apply_dense", "rows": rows, "k": k, "lower_triangular": bool(lower),
+                          "ms": ms, "rel_err_vs_torch": err,
+                          "tflops": 2.0 * needed / 8 * k / (ms * 1e-3) / 1e12,
                           "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s",
-                                       "frac": gbs / hbm, "peak_source": src},
+                                       "frac": gbs / hbm, "peak_source": src,
+                                       "algorithmic_bytes": needed},
                           "l2": "matrix (4.9 GB) larger than L2"}))
         del T
-
 
 if __name__ == "__main__":
     main()
