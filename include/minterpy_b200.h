@@ -111,7 +111,10 @@ int mpx_eval(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
  *     call at BASELINE config 2.  Beyond that the call returns MPX_ERR_UNSUPPORTED and does
  *     nothing -- split k, or use mpx_eval.
  *   - the first call on a device looks the array's address up (set-up); make that first call
- *     before starting any stream capture.
+ *     before starting any stream capture, and before the application takes all device memory:
+ *     with the runtime's default lazy module loading the array is only placed on the GPU at
+ *     that moment (or run with CUDA_MODULE_LOADING=EAGER).  A set-up that finds no memory left
+ *     returns MPX_ERR_NOMEM.
  *   - the array is shared by all plans and calls on the device and keeps the last call's
  *     contents; each call rewrites every slot it reads, so nothing needs clearing, but two
  *     calls whose kernels overlap on the GPU overwrite each other's coefficients: serialise
@@ -184,8 +187,10 @@ int mpx_apply_dense_ex(int device, const double *T, int64_t rows, int64_t cols, 
  * mpx_eval; unlike the reference, k > 1 coefficient columns are accepted.  The derivative of a
  * product table entry prod_{t<q}(x - g_t) is formed by the product-rule recurrence (O(q * order)
  * flops) instead of the reference's sum over itertools.combinations, so values agree up to
- * rounding, not bit for bit.  MPX_ERR_UNSUPPORTED when m > 8 or the per-point tables of the
- * index set do not fit shared memory.
+ * rounding, not bit for bit.  Few polynomials (k below MPX_INFO_MMA_MIN_K) run on the tree kernel
+ * with differentiated tables (plan-owned scratch for the tables of dimensions >= 2, one stream
+ * at a time like mpx_eval); more on the tensor-core kernel, which reports MPX_ERR_UNSUPPORTED
+ * when m > 8 or the per-point tables of the index set do not fit shared memory.
  */
 int mpx_eval_deriv(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
                    const double *coeffs, int k, int64_t ld_c, const int32_t *orders_h,

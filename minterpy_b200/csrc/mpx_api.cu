@@ -52,6 +52,14 @@ extern "C" int mpx_eval_deriv(mpx_plan *pl, const double *xx, int64_t P, int64_t
     if (P == 0) return MPX_OK;
     if (!xx || !coeffs || !out) return mpx_fail(MPX_ERR_ARG, "null device pointer");
     if (ld_xx < pl->m || ld_c < k || ld_out < k) return mpx_fail(MPX_ERR_ARG, "leading dimension too small");
+    if (pl->tree_ok && !mpx_mma_eligible(pl, k)) {
+        // few polynomials: the tree kernel with differentiated tables (mpx_eval_deriv.cu)
+        DeviceGuard dgt(pl->device);
+        if (!dgt.ok) return mpx_fail(MPX_ERR_CUDA, "cannot select the plan's CUDA device");
+        std::lock_guard<std::mutex> lock(pl->mu);
+        return mpx_launch_eval_tree_deriv(pl, &pl->image, &pl->deriv_tables, xx, P, ld_xx, coeffs, k,
+                                          ld_c, orders, out, ld_out, (cudaStream_t)stream);
+    }
     if (!mpx_mma_fits(pl, k))
         return mpx_fail(MPX_ERR_UNSUPPORTED,
                         "derivative evaluation runs on the shared-memory-table kernel: m <= 8 and "

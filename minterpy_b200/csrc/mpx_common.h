@@ -173,6 +173,7 @@ struct mpx_plan {
     // own one, so a NumPy call can never repack what a tensor call is still reading
     std::mutex mu;                   // host-side state of `image` (pointer, size, event)
     MpxImage image;                  // mpx_eval / mpx_eval_deriv
+    MpxImage deriv_tables;           // mpx_eval_deriv on the tree kernel: tables of dimensions >= 2
     std::mutex host_mu;              // one host-buffer call per plan at a time (held to the end)
     MpxImage host_image;             // mpx_eval_host
     // staging for the host-buffer entry points: two streams, device blocks for points and
@@ -251,6 +252,10 @@ size_t mpx_tmma_scratch_bytes(const mpx_plan *plan, int k);
 int mpx_launch_eval_tmma(mpx_plan *plan, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,
                          const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
                          cudaStream_t stream);
+// few polynomials: partial derivative on the tree kernel, mpx_eval_deriv.cu
+int mpx_launch_eval_tree_deriv(mpx_plan *plan, MpxImage *img, MpxImage *tables, const double *xx,
+                               int64_t P, int64_t ld_xx, const double *coeffs, int k, int64_t ld_c,
+                               const int *orders_h, double *out, int64_t ld_out, cudaStream_t stream);
 extern int mpx_test_eval_stages;   // test hook, mpx_eval.cu
 // bytes of plan scratch an evaluation of k polynomials needs (either path)
 size_t mpx_eval_scratch_bytes(const mpx_plan *plan, int k);

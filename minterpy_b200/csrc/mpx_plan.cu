@@ -709,6 +709,7 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
     cudaFree(pl->d_exp64);
     mpx_image_destroy(&pl->image);
     mpx_image_destroy(&pl->host_image);
+    mpx_image_destroy(&pl->deriv_tables);
     for (int b = 0; b < 2; ++b) {
         cudaFree(pl->h_x[b]);
         cudaFree(pl->h_o[b]);

@@ -140,11 +140,20 @@ def test_derivative_argument_errors(mpb, nxt):
         api.deriv_newt_eval(x, c, e, gp, np.array([1.0, 0.0]))
     with pytest.raises(ValueError):
         api.deriv_newt_eval(x, c[:-1], e, gp, np.array([1, 0]))
-    # more than 8 dimensions: no table kernel, and it says so
-    e9 = np.zeros((1, 9), dtype=np.int64)
-    with pytest.raises(NotImplementedError):
-        api.deriv_newt_eval(np.zeros((2, 9)), np.ones(1), e9, np.zeros((1, 9)),
-                            np.ones(9, dtype=np.int64))
+    # more than 8 dimensions (no shared-memory-table kernel): few polynomials run on the tree
+    # kernel with differentiated tables -- x0 * x8 differentiated along both is 1, along x1 is 0
+    e9 = np.zeros((4, 9), dtype=np.int64)
+    e9[1, 0] = e9[2, 8] = e9[3, 0] = e9[3, 8] = 1
+    gp9 = np.tile(np.array([[1.0], [-1.0]]), (1, 9))
+    c9 = np.array([0.0, 0.0, 0.0, 1.0])                     # (x0 - 1)(x8 - 1)
+    x9 = np.random.default_rng(3).uniform(-1, 1, (5, 9))
+    o = np.zeros(9, dtype=np.int64)
+    o[0] = o[8] = 1
+    assert np.allclose(api.deriv_newt_eval(x9, c9, e9, gp9, o), 1.0, rtol=0, atol=1e-15)
+    o[8] = 0
+    assert np.allclose(api.deriv_newt_eval(x9, c9, e9, gp9, o), x9[:, 8] - 1.0, rtol=0, atol=1e-15)
+    o[1] = 1
+    assert np.array_equal(api.deriv_newt_eval(x9, c9, e9, gp9, o), np.zeros(5))
 
 
 # ---- regression ---------------------------------------------------------------------------------

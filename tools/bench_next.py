@@ -45,6 +45,7 @@ def host_ms(fn, iters=5):
 def main():
     import torch
     import minterpy_b200 as mpb
+    from minterpy_b200 import _lib
     from minterpy_b200 import api, generators
     from minterpy_b200.polynomials import is_lexicographically_complete
     from minterpy_b200.regression import compute_regression_matrix
@@ -62,7 +63,8 @@ def main():
                                   "169 s at (5,12,2.0) (SURVEY.md 8f)"}))
 
     # ---- derivative evaluation ---------------------------------------------------------------
-    for tag, P, k, orders in (("cfg2", 1_000_000, 1, (1, 0, 0, 0)), ("cfg2", 1_000_000, 8, (1, 0, 2, 0)),
+    for tag, P, k, orders in (("cfg2", 1_000_000, 1, (1, 0, 0, 0)), ("cfg2", 1_000_000, 1, (0, 1, 2, 1)),
+                              ("cfg2", 1_000_000, 8, (1, 0, 2, 0)), ("cfg5", 1_000_000, 1, (2, 0, 1)),
                               ("cfg3", 1_000_000, 64, (1, 0, 0, 0, 0, 1))):
         g = golden_io.load(tag)
         e, gp = g["exponents"], g["generating_points"]
@@ -77,8 +79,9 @@ def main():
                           "ms": ms, "pm_per_s": P * N / (ms * 1e-3),
                           "tensor_tflops": 2.0 * P * N * max(k, 8) / (ms * 1e-3) / 1e12,
                           "plain_eval_ms": ms0,
-                          "kernel": "shared-memory-table tensor kernel (mpx_eval_mma.cu), "
-                                    "polynomial columns padded to 8"}))
+                          "kernel": ("shared-memory-table tensor kernel (mpx_eval_mma.cu)"
+                                     if k >= plan.info(_lib.INFO_MMA_MIN_K) > 0 else
+                                     "tree kernel with differentiated tables (mpx_eval_deriv.cu)")}))
 
     # ---- NewtonPolynomial.diff (derivative at the nodes + divided differences) -------------
     for tag in ("cfg2", "cfg4"):
