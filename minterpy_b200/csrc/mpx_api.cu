@@ -292,8 +292,9 @@ extern "C" int mpx_eval_host(mpx_plan *pl, const double *xx_h, int64_t P, int64_
     block = std::max<int64_t>(block, (int64_t)1 << 16);
     block = std::min(block, P);
     const int nbuf = (P > block) ? 2 : 1;
-    const bool stage_x = is_pageable(xx_h) && (size_t)P * m * 8 >= ((size_t)1 << 20);
-    const bool stage_o = is_pageable(out_h) && (size_t)P * k * 8 >= ((size_t)1 << 20);
+    // (below 16 MiB the driver's own staging of a pageable copy is as fast as ours)
+    const bool stage_x = is_pageable(xx_h) && (size_t)P * m * 8 >= ((size_t)16 << 20);
+    const bool stage_o = is_pageable(out_h) && (size_t)P * k * 8 >= ((size_t)16 << 20);
     if ((rc = ensure_host_streams(pl)) != MPX_OK) return rc;
     if ((rc = grow(&pl->h_c, &pl->h_c_cap, (size_t)pl->N * k * 8)) != MPX_OK) return rc;
     for (int b = 0; b < nbuf; ++b) {
@@ -380,7 +381,7 @@ extern "C" int mpx_dds_host(mpx_plan *pl, const double *in_h, int k, int64_t ld_
     if ((rc = ensure_host_streams(pl)) != MPX_OK) return rc;
     if ((rc = grow(&pl->h_v, &pl->h_v_cap, (size_t)N * k * 8)) != MPX_OK) return rc;
 
-    const bool big = (size_t)N * k * 8 >= ((size_t)1 << 20);
+    const bool big = (size_t)N * k * 8 >= ((size_t)16 << 20);
     const bool stage_i = big && is_pageable(in_h);
     const bool stage_o = big && is_pageable(out_h);
     int status = MPX_OK;

@@ -260,18 +260,26 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
                         double *ut = ups + (size_t)(u - 1) * PS + pbase;
                         const bool top = (u == nf - 1);
                         const double gu = gps[(2 + u) * p.gp_rows + (int)w1];
+                        // the 4 lanes of a point compute and store identical values to the same
+                        // words: all of them read first, the warp meets, then they store -- a lane
+                        // that lags behind (thread 0 polls the ring in this loop) must not read
+                        // what a faster lane has already restarted
+                        double tvv[MT], avv[MT];
 #pragma unroll
                         for (int mt = 0; mt < MT; ++mt) {
-                            // the 4 lanes of a point compute and store identical values
-                            const double tv = ut[8 * mt];
-                            const double av = fma(tv, low[mt], ut[up_stride + 8 * mt]);
+                            tvv[mt] = ut[8 * mt];
+                            avv[mt] = fma(tvv[mt], low[mt], ut[up_stride + 8 * mt]);
+                        }
+                        __syncwarp();
+#pragma unroll
+                        for (int mt = 0; mt < MT; ++mt) {
                             if (!top) {
-                                low[mt] = av;
+                                low[mt] = avv[mt];
                                 ut[up_stride + 8 * mt] = 0.0;
                                 ut[8 * mt] = 1.0;
                             } else {
-                                ut[up_stride + 8 * mt] = av;
-                                if (!last) ut[8 * mt] = tv * (xs[(size_t)u * PS + pbase + 8 * mt] - gu);
+                                ut[up_stride + 8 * mt] = avv[mt];
+                                if (!last) ut[8 * mt] = tvv[mt] * (xs[(size_t)u * PS + pbase + 8 * mt] - gu);
                             }
                         }
                         __syncwarp();
