@@ -1,23 +1,33 @@
 #!/usr/bin/env python
 """Benchmark of the Newton-evaluation hot path (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--scaling weak|strong]
+                  [--impl reference]
 
 One "step" = one pass of the evaluation kernel over one batch of synthetic query points.
-At N = 1 the workload is BASELINE config 2 (m=4, n=16, lp=2, 1e8 points); with N > 1 (torchrun,
-one rank per GPU) every rank evaluates its own 1e8-point shard (weak scaling, no data-path
-collective; the coefficients are broadcast once over NCCL before the timed region).
+At N = 1 the workload is BASELINE config 2 (m=4, n=16, lp=2, 1e8 points).  With N > 1 (torchrun,
+one rank per GPU):
+  --scaling weak   (default) every rank evaluates its own shard of the workload's size (no
+                   data-path collective; the coefficients are broadcast once over NCCL before
+                   the timed region);
+  --scaling strong ONE job -- the workload's points (cfg5: 1e9, as BASELINE config 5 is written)
+                   split over the ranks.
 
-value  = point x monomial evaluations per second, inputs resident in HBM (CUDA events on the
-         launching stream, max over ranks);
-e2e    = the same metric through the public NumPy API with pinned HOST buffers (H2D of the
-         points and D2H of the values inside the timed region);
+value  = point x monomial evaluations per second of the whole job, inputs resident in HBM (CUDA
+         events on the launching stream, max over ranks);
+e2e    = the same metric through the public API with HOST buffers: page-locked NumPy arrays
+         (H2D of the points and D2H of the values inside the timed region); `e2e_pageable` the
+         same with an ordinary NumPy array.  Strong scaling with N > 1: the whole job per step --
+         NCCL broadcast of the coefficients, upload of the shard, evaluation, all_gather of the
+         result shards, download;
 roofline = executed FP64 flops of the evaluation kernel / its CUDA-event duration, against
-         the DFMA peak measured on this box by tools/fp64_peak.cu (MEASURED_PEAKS.json has no
-         FP64 figure) -- nominal 37.2 TFLOP/s is reported beside it;
-cpu_baseline = the CPU oracle (a C restatement of the reference's algorithm, all host
-         threads) on a bounded sample of the same workload.
-`--impl reference` times only that CPU path.
+         the DFMA (or DMMA) rate measured on this box by tools/fp64_peak.cu (MEASURED_PEAKS.json
+         has no FP64 figure) -- nominal 37.2 TFLOP/s is reported beside it;
+cpu_baseline = the UNMODIFIED reference (baseline/_ref, tools/make_baseline_ref.py) on a bounded
+         sample of the same workload: its eval_newton_polynomials as-is in one process and over
+         point shards in one forked process per host core; the C port of the oracle beside it,
+         and instead of it if the reference does not import (the line then says why).
+`--impl reference` times only that CPU path (rank 0; the other ranks exit).
 """
 import argparse
 import json
