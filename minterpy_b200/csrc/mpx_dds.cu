@@ -478,10 +478,11 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     if (f >= n_work) return;
     constexpr int C = 2 * H;
     const int64_t col0 = (int64_t)blockIdx.y * (32 * C) + 2 * lane;      // pair h starts at col0 + 64 h
+    // pairs of this lane that exist (k may end inside the warp's column block); a lane without
+    // any still takes part: it hands rows to the TMA and sweeps zeros
     unsigned active = 0;
 #pragma unroll
     for (int h = 0; h < H; ++h) active |= (col0 + 64 * h < k) ? 1u << h : 0u;
-    if (!active) return;
     const int o = woff[f];
     const int len = woff[f + 1] - o;
     const int32_t *rows = wrows + o;

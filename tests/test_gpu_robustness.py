@@ -245,3 +245,51 @@ def test_regression_on_a_set_with_holes_with_tensors(mpb, nxt_rows):
 @pytest.fixture(scope="module")
 def nxt_rows():
     return golden_io.load("next_rows")
+
+
+def _same_bits(a, b):
+    return np.array_equal(np.ascontiguousarray(a).view(np.uint64), np.ascontiguousarray(b).view(np.uint64))
+
+
+def test_dds_kernels_agree_bit_for_bit_on_ragged_widths_and_special_values(mpb, golden_cfg, golden_small):
+    """The several-columns-per-lane dds kernel (default for k >= 64) against the
+    one-column-per-lane kernel (test hook), bit patterns compared: column counts that leave the
+    last column block ragged or nearly empty, and values the fast division must not take --
+    zeros of both signs, equal neighbours, subnormals, huge numbers, inf and nan -- which send
+    single lanes through the redo path."""
+    import torch
+    from minterpy_b200 import _lib
+    lib = _lib.lib()
+    rng = np.random.default_rng(123)
+    cases = [("cfg2", golden_cfg("cfg2")), ("cfg5", golden_cfg("cfg5")), ("cfg3", golden_cfg("cfg3"))]
+    small = golden_small
+    cases.append(("m3_n4_lpinf", {"exponents": small["m3_n4_lpinf/exponents"],
+                                  "generating_points": small["m3_n4_lpinf/generating_points"]}))
+    for tag, g in cases:
+        e, gp = g["exponents"], g["generating_points"]
+        N = e.shape[0]
+        plan = mpb.get_plan(e, gp)
+        for k in (64, 66, 100, 128, 130, 190, 254, 256, 320):
+            vals = rng.uniform(-1, 1, (N, k))
+            special = k in (66, 130, 256)
+            if special:
+                idx = rng.integers(0, N, 40)
+                col = rng.integers(0, k, 40)
+                vals[idx[:8], col[:8]] = 0.0
+                vals[idx[8:12], col[8:12]] = -0.0
+                vals[idx[12:16], col[12:16]] = 1e-310
+                vals[idx[16:20], col[16:20]] = 1e300
+                vals[idx[20:22], col[20:22]] = np.inf
+                vals[idx[22:24], col[22:24]] = np.nan
+                vals[:, 3] = 0.25                               # a constant column: all zeros after
+                vals[:, 5] = 0.0
+            v = torch.as_tensor(vals, device="cuda")
+            got = plan.dds(v).cpu().numpy()
+            lib.mpx_debug_set_dds_group(2)                      # one column per lane
+            try:
+                want = plan.dds(v).cpu().numpy()
+            finally:
+                lib.mpx_debug_set_dds_group(0)
+            assert _same_bits(got, want), (tag, k)
+            if not special:
+                assert np.array_equal(got[:, :2], oracle.dds(np.ascontiguousarray(vals[:, :2]), e, gp)), (tag, k)

@@ -25,12 +25,25 @@ REFERENCE = "/root/reference"
 TARGET = os.path.join(ROOT, "baseline", "_ref")
 
 
+def _make_writable(top):
+    for root, dirs, files in os.walk(top):
+        for name in dirs + files:
+            path = os.path.join(root, name)
+            try:
+                os.chmod(path, os.stat(path).st_mode | 0o200)
+            except OSError:
+                pass
+    if os.path.isdir(top):
+        os.chmod(top, os.stat(top).st_mode | 0o200)
+
+
 def make(force=False):
     """Returns TARGET, or None when /root/reference is absent (GPU box: prebuilt copy is used)."""
     if not os.path.isdir(os.path.join(REFERENCE, "src", "minterpy")):
         return TARGET if os.path.isdir(os.path.join(TARGET, "minterpy")) else None
     if os.path.isdir(os.path.join(TARGET, "minterpy")) and not force:
         return TARGET
+    _make_writable(TARGET)
     shutil.rmtree(TARGET, ignore_errors=True)
     os.makedirs(TARGET, exist_ok=True)
     with tempfile.TemporaryDirectory() as tmp:
@@ -41,6 +54,7 @@ def make(force=False):
                                "/opt/wheelhouse", "--target", TARGET, src])
     shutil.copytree(os.path.join(REFERENCE, "tests"), os.path.join(TARGET, "reference_tests"),
                     ignore=shutil.ignore_patterns("__pycache__"))
+    _make_writable(TARGET)          # the checkout is read-only; the copy need not be
     return TARGET
 
 
