@@ -591,7 +591,8 @@ def main():
                                "eval_tmma_kernel" if tensor_path else "eval_tree_kernel"),
                     "kernel_ms": kernel_ms,
                     "hbm_gbs": P * 8 * (m + k) / (kernel_ms * 1e-3) / 1e9}
-        cpu = None if args.no_cpu else cpu_baseline_subprocess(args.workload, args.cpu_seconds or 12.0)
+        # (rank 0 at N = 1 only: with N > 1 the driver's reference arm carries the CPU figure)
+        cpu = None if (args.no_cpu or world > 1) else cpu_baseline_subprocess(args.workload, args.cpu_seconds or 12.0)
         cfgd = workload_config(args, N, k, desc, m, world)
         line = {"metric": "newton_evals_per_sec", "value": value, "unit": "point*monomials/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
