@@ -160,7 +160,13 @@ public:
     // run fn(part) for part = 0..parts-1 on the helpers and the calling thread
     void run(int parts, const std::function<void(int)> &fn)
     {
-        std::lock_guard<std::mutex> one_job(gate);
+        // the pool is busy with another caller's block (several GPUs fed from one process):
+        // this thread copies its block alone rather than queue behind it
+        std::unique_lock<std::mutex> one_job(gate, std::try_to_lock);
+        if (!one_job.owns_lock()) {
+            for (int p = 0; p < parts; ++p) fn(p);
+            return;
+        }
         {
             std::lock_guard<std::mutex> lk(mu);
             job = &fn;

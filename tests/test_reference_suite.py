@@ -29,7 +29,10 @@ needs_reference = pytest.mark.skipif(
     reason="reference not available (run tools/make_baseline_ref.py where /root/reference exists)")
 
 
-def run_suite(mode, timeout):
+def run_suite(mode, timeout, files=None, expect=None):
+    """Run reference test files in a child pytest; returns (passed, sorted failing test ids).
+    With `expect` the run must pass completely with that many cases."""
+    files = HOT_PATH_FILES if files is None else files
     tests_dir = reference_tests_dir()
     env = dict(os.environ)
     env["MPX_REF_SUITE_PLAN"] = mode
@@ -39,26 +42,45 @@ def run_suite(mode, timeout):
     with tempfile.TemporaryDirectory() as tmp:
         # copies: the child must not pick up the reference's setup.cfg (coverage options) nor
         # write __pycache__ / .pytest_cache beside the reference
-        for f in HOT_PATH_FILES + ["conftest.py"]:
+        for f in files + ["conftest.py"]:
             with open(os.path.join(tests_dir, f)) as src, open(os.path.join(tmp, f), "w") as dst:
                 dst.write(src.read())
         ini = os.path.join(tmp, "pytest.ini")
         with open(ini, "w") as f:
             f.write("[pytest]\n")
-        cmd = [sys.executable, "-m", "pytest", "-q", "-p", "ref_suite_plugin", "-p",
+        cmd = [sys.executable, "-m", "pytest", "-q", "-rf", "-p", "ref_suite_plugin", "-p",
                "no:cacheprovider", "-c", ini, "--rootdir", tmp] + \
-              [os.path.join(tmp, f) for f in HOT_PATH_FILES]
+              [os.path.join(tmp, f) for f in files]
         res = subprocess.run(cmd, env=env, cwd=tmp, capture_output=True, text=True, timeout=timeout)
     tail = "\n".join((res.stdout + res.stderr).splitlines()[-40:])
     summary = re.search(r"(\d+) passed", res.stdout)
-    failed = re.search(r"(\d+) (failed|error)", res.stdout)
-    assert res.returncode == 0 and failed is None, tail
-    assert summary and int(summary.group(1)) == N_CASES, tail
+    failing = sorted(set(re.findall(r"^(?:FAILED|ERROR) (\S+)", res.stdout, flags=re.M)))
+    assert summary, tail
+    if expect is not None:
+        assert res.returncode == 0 and not failing, tail
+        assert int(summary.group(1)) == expect, tail
+    return int(summary.group(1)), [f.split("/")[-1] for f in failing]
+
+
+def all_reference_test_files():
+    return sorted(f for f in os.listdir(reference_tests_dir()) if f.startswith("test_") and f.endswith(".py"))
 
 
 @needs_reference
 def test_reference_hot_path_suite_with_install_on_cpu():
-    run_suite("oracle", timeout=1500)
+    run_suite("oracle", timeout=1500, expect=N_CASES)
+
+
+@needs_reference
+def test_whole_reference_suite_changes_nothing_else_on_cpu():
+    """Every test file of the reference (2250 cases): with install() exactly the cases fail that
+    fail in the unpatched reference in this environment (its GMRES solver cases under the
+    installed SciPy), nothing else, and as many pass."""
+    files = all_reference_test_files()
+    passed_plain, failing_plain = run_suite("unpatched", timeout=1500, files=files)
+    passed, failing = run_suite("oracle", timeout=1500, files=files)
+    assert failing == failing_plain
+    assert passed == passed_plain and passed >= 2000
 
 
 @needs_reference
@@ -66,4 +88,16 @@ def test_reference_hot_path_suite_with_install_on_cpu():
 def test_reference_hot_path_suite_with_install_on_gpu():
     import torch
     assert torch.cuda.is_available()
-    run_suite("cuda", timeout=2400)
+    run_suite("cuda", timeout=2400, expect=N_CASES)
+
+
+@needs_reference
+@pytest.mark.gpu
+def test_whole_reference_suite_changes_nothing_else_on_gpu():
+    import torch
+    assert torch.cuda.is_available()
+    files = all_reference_test_files()
+    passed_plain, failing_plain = run_suite("unpatched", timeout=1500, files=files)
+    passed, failing = run_suite("cuda", timeout=2400, files=files)
+    assert failing == failing_plain
+    assert passed == passed_plain and passed >= 2000
