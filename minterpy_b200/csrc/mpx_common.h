@@ -59,7 +59,8 @@ struct EvalProgram {
 // contraction [points x e0] * [e0 x leaves] that DMMA m8n8k4 computes 8 leaves at a time.  A
 // TILE is 8 columns (leaves with consecutive dimension-1 exponents; the columns may continue
 // into the head of the next (e2.., e_{m-1}) group) and `ks` k-steps of 4 dimension-0
-// exponents; its coefficients are stored as B fragments: slot = s*32 + column*4 + (e0 & 3).
+// exponents; its coefficients are stored as B fragments, two k-steps interleaved so that one 16-byte
+// load feeds both: slot = (s/2)*64 + (column*4 + (e0 & 3))*2 + (s & 1).
 // Tile record, two words:
 //   w0 bits 0..4 ks | 5..8 columns of the current group | 9..12 columns of the next group |
 //      13..20 dimension-1 exponent of column 0 | 21 the current group ends in this tile |

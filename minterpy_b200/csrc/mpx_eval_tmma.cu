@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
         }
         mbar_wait(&full[s], ph);
         const uint32_t *dw = reinterpret_cast<const uint32_t *>(ring + s * T_STAGE_BYTES);
-        uint32_t cf = smem_u32(ring + s * T_STAGE_BYTES + MPX_T_DESC_WORDS * 4) + 8u * lane;
+        uint32_t cf = smem_u32(ring + s * T_STAGE_BYTES + MPX_T_DESC_WORDS * 4) + 16u * lane;
         const int iend = MPX_DESC_HDR + (int)dw[0];
         for (int i = MPX_DESC_HDR; i < iend; i += 2) {
             if (next_load < p.n_chunks) {            // thread 0, between tiles
@@ -211,14 +211,22 @@ __global__ void __launch_bounds__(32 * NW, MINB) eval_tmma_kernel(const TmmaPara
 #pragma unroll
             for (int mt = 0; mt < MT; ++mt) cacc[mt][0] = cacc[mt][1] = 0.0;
 #pragma unroll
-            for (int st = 0; st < KS0; ++st) {
-                if (st < ks) {
-                    const double b = lds64(cf + 256 * st);
+            for (int sp = 0; sp < (KS0 + 1) / 2; ++sp) {
+                if (2 * sp < ks) {
+                    // B fragments of two k-steps in one 16-byte load (conflict free)
+                    const double2 b = lds128(cf + 512 * sp);
 #pragma unroll
-                    for (int mt = 0; mt < MT; ++mt) dmma884(cacc[mt][0], cacc[mt][1], a[st][mt], b);
+                    for (int mt = 0; mt < MT; ++mt) dmma884(cacc[mt][0], cacc[mt][1], a[2 * sp][mt], b.x);
+                    {
+                        if (2 * sp + 1 < KS0 && 2 * sp + 1 < ks) {
+#pragma unroll
+                            for (int mt = 0; mt < MT; ++mt)
+                                dmma884(cacc[mt][0], cacc[mt][1], a[(2 * sp + 1 < KS0) ? 2 * sp + 1 : 0][mt], b.y);
+                        }
+                    }
                 }
             }
-            cf += 256u * ks;
+            cf += 512u * (uint32_t)((ks + 1) >> 1);
             // epilogue: this lane holds columns 2*jl and 2*jl+1 of its 4 points.  Columns that
             // are not part of the current group read the zero row of T1.
 #pragma unroll

@@ -298,16 +298,17 @@ void compile_tile_program(const int64_t *e, int64_t N, int m, TileProgram &tp)
                 adv_exp = (int)cur[D];
             }
         }
-        if (coef_used + ks * 32 > MPX_T_COEF_CAP ||
+        const int kpairs = (ks + 1) / 2;     // k-steps are stored in pairs: one LDS.128 feeds two
+        if (coef_used + kpairs * 64 > MPX_T_COEF_CAP ||
             (int)words.size() + 2 > MPX_T_DESC_WORDS - MPX_DESC_HDR)
             flush();
         int32_t *slots = tp.slot_src.data() + (size_t)tp.n_chunks * MPX_T_COEF_CAP + coef_used;
         for (int c = 0; c < ncur + nnext; ++c) {
             const Leaf &lf = leaves[i + c];
             for (int e0 = 0; e0 < lf.len; ++e0)
-                slots[(e0 >> 2) * 32 + c * 4 + (e0 & 3)] = (int32_t)(lf.first + e0);
+                slots[(e0 >> 3) * 64 + (c * 4 + (e0 & 3)) * 2 + ((e0 >> 2) & 1)] = (int32_t)(lf.first + e0);
         }
-        coef_used += ks * 32;
+        coef_used += kpairs * 64;
         const int e1 = (m >= 2) ? (int)cur[1] : 0;
         words.push_back((uint32_t)ks | ((uint32_t)ncur << 5) | ((uint32_t)nnext << 9) |
                         ((uint32_t)e1 << 13) | ((uint32_t)ends << 21) | ((uint32_t)nf << 22) |

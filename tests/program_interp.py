@@ -158,9 +158,9 @@ def run_tile_program(desc, slots, x, coeffs, exponents, gp):
             for s in range(ks):                       # one mma k-step: 4 exponents x 8 columns
                 for col in range(8):
                     for q in range(4):
-                        C[col] += packed[cp + s * 32 + col * 4 + q] * T0[4 * s + q]
+                        C[col] += packed[cp + (s >> 1) * 64 + (col * 4 + q) * 2 + (s & 1)] * T0[4 * s + q]
             fma += 32 * ks
-            cp += 32 * ks
+            cp += 64 * ((ks + 1) // 2)
             for col in range(8):
                 if col < ncur:
                     acc_cur += T1[e1 + col] * C[col]
