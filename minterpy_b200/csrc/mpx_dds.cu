@@ -513,7 +513,7 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     bool bad = false;
     // Row-blocked sweep (see dds_fiber_kernel): element r receives its updates i = 1..r in order,
     // each with the final value of element i-1; four rows advance together.
-#ifdef MPX_DDS_PROBE_NO_SWEEP
+#ifdef MPX_DDS_PROBE_NO_SWEEP     // probe build: gather and scatter only
     int r = len;
 #else
     int r = 1;
@@ -600,7 +600,7 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
 #pragma unroll
             for (int h = 0; h < H; ++h) bl[((r + q) * H + h) * 32] = x[q][h];
     }
-#ifndef MPX_DDS_PROBE_NO_REDO
+#ifndef MPX_DDS_PROBE_NO_REDO     // probe build: sweep without the true-division fallback
     if (bad) dds_redo_columns<H>(bl, vals, ld, col0, active, rows, len, gcol);
 #endif
     // Write back rows 1..len-1 (element 0 of a fiber never changes), again one bulk copy per row
@@ -611,6 +611,7 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     bulk_commit_and_wait_read();          // the buffer must outlive the copies that read it
 }
 
+#ifdef MPX_TUNING   // measured and dropped: built for the lab bench only
 // ---- register-resident fibers (all fibers of the dimension at most MPX_DDS_REG_LEN long) -------
 // One warp per fiber, lane = value column, one pass per dimension like the kernel above, but the
 // fiber never touches shared memory: a lane keeps its column of the fiber in registers, the code
@@ -718,6 +719,8 @@ dds_fiber_reg_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_t
     }
 }
 
+#endif  // MPX_TUNING
+
 }  // namespace
 
 // several columns per lane: k, ld and the base address must allow 16-byte accesses, fibers <= 40
@@ -775,6 +778,7 @@ static int launch_dds_cols(mpx_plan *pl, double *vals, int k, int64_t ld, cudaSt
 #endif
 }
 
+#ifdef MPX_TUNING
 // register-resident fibers: every dimension with work must have max_len <= MPX_DDS_REG_LEN
 static int launch_dds_registers(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
                                 bool *handled)
@@ -799,6 +803,8 @@ static int launch_dds_registers(mpx_plan *pl, double *vals, int k, int64_t ld, c
     *handled = true;
     return MPX_OK;
 }
+
+#endif  // MPX_TUNING
 
 template <int FW>
 static int launch_dds_fibers_fw(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
@@ -913,10 +919,12 @@ int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t s
             rc = launch_dds_cols(pl, vals, k, ld, stream, &handled);
             if (rc != MPX_OK || handled) return rc;
         }
+#ifdef MPX_TUNING
         if (mode && strcmp(mode, "registers") == 0) {
             rc = launch_dds_registers(pl, vals, k, ld, stream, &handled);
             if (rc != MPX_OK || handled) return rc;
         }
+#endif
         rc = launch_dds_fibers(pl, vals, k, ld, stream, &handled);
         if (rc != MPX_OK || handled) return rc;
     }
