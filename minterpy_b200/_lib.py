@@ -46,6 +46,7 @@ DEBUG_SIGNATURES = {
     "mpx_debug_set_tmma": (None, [c_int]),          # at plan creation: 0 auto, 1 force, 2 never
     "mpx_debug_set_dds_group": (None, [c_int]),     # dds through the fused slice kernel
     "mpx_debug_set_eval_stages": (None, [c_int]),   # ring depth of the tree kernel (0 = default)
+    "mpx_debug_set_eval_uniform": (None, [c_int]),  # 2: record stream from the ring, never as a parameter
 }
 
 MPX_DENSE_LOWER = 1

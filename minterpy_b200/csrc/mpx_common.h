@@ -45,6 +45,16 @@ inline int mpx_l0p_for(int max_exp0)
 }
 inline int mpx_count_words(int l0p) { return (l0p / 2 + 7) / 8; }
 
+// The used words of the record stream, for kernels that take the program as a KERNEL PARAMETER
+// (constant bank, read through the uniform datapath): per chunk the header and the words it
+// uses, chunk c at w[off[c]].  16.9 KB of the 32 KB a launch may carry.
+constexpr int MPX_U_WORDS = 4096;
+constexpr int MPX_U_CHUNKS = 127;
+struct MpxUniformProgram {
+    uint32_t off[MPX_U_CHUNKS + 1];
+    uint32_t w[MPX_U_WORDS];
+};
+
 struct EvalProgram {
     int n_chunks = 0;
     int64_t n_leaves = 0;
@@ -154,6 +164,7 @@ struct mpx_plan {
     bool tree_ok = true;             // dimension-0 exponents fit the register table of the tree kernel
     // evaluation
     EvalProgram prog;
+    std::vector<MpxUniformProgram> uprog;   // one element if the record stream qualifies, else empty
     TileProgram tprog;               // tensor-core tree kernel (complete sets)
     uint32_t *d_tdesc = nullptr;
     int32_t *d_tslot_src = nullptr;
@@ -258,5 +269,6 @@ int mpx_launch_eval_tree_deriv(mpx_plan *plan, MpxImage *img, MpxImage *tables, 
                                int64_t P, int64_t ld_xx, const double *coeffs, int k, int64_t ld_c,
                                const int *orders_h, double *out, int64_t ld_out, cudaStream_t stream);
 extern int mpx_test_eval_stages;   // test hook, mpx_eval.cu
+extern int mpx_test_eval_uniform;  // test hook, mpx_eval.cu: 2 = never take the uniform-program kernels
 // bytes of plan scratch an evaluation of k polynomials needs (either path)
 size_t mpx_eval_scratch_bytes(const mpx_plan *plan, int k);

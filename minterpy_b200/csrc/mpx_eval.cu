@@ -41,6 +41,8 @@ int mpx_launch_eval(mpx_plan *pl, MpxImage *img, const double *xx, int64_t P, in
 // variant.
 int mpx_test_eval_stages = 0;
 extern "C" void mpx_debug_set_eval_stages(int stages) { mpx_test_eval_stages = stages; }
+int mpx_test_eval_uniform = 0;
+extern "C" void mpx_debug_set_eval_uniform(int mode) { mpx_test_eval_uniform = mode; }
 
 size_t mpx_eval_scratch_bytes(const mpx_plan *pl, int k)
 {

@@ -3,6 +3,7 @@
 #pragma once
 #include <cstdio>
 #include <cstdlib>
+#include <type_traits>
 
 #include "mpx_common.h"
 #include "mpx_ptx.h"
@@ -151,9 +152,17 @@ struct LengthChain {
 //   then gp (m*gp_rows doubles), T1 ((max_exp1+1)*R*NT doubles),
 //   running product / partial sum of dimensions 3.. (2 * (U-1) * R * NT doubles; dimension 2
 //   keeps its pair in registers)
-template <int L0P, int R, int A, int NT, int MINB, bool DERIV>
-__global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
+// UP = MpxUniformProgram: the record words come from a kernel parameter (constant bank) instead
+// of the shared-memory ring and records have a fixed size, so everything the control flow of the
+// leaf loops depends on -- counts, fold flags, loop bounds -- is provably warp-uniform: ptxas
+// keeps it in uniform registers and branches uniformly (BRA.U, no BSSY/BSYNC brackets).  That
+// only happens if the warp does not spin on the ring's mbarrier with all 32 lanes (a per-thread
+// loop exit makes ptxas treat what follows as divergent): lane 0 waits, the warp meets.
+struct NoUniformProgram {};
+template <int L0P, int R, int A, int NT, bool DERIV, class UP>
+__device__ __forceinline__ void eval_tree_body(const EvalParams &p, const UP &up)
 {
+    constexpr bool UDESC = !std::is_same<UP, NoUniformProgram>::value;
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int NCW = (L0P / 2 + 7) / 8;
     using T1L = T1Layout<R, NT>;
@@ -318,11 +327,26 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                 if (++next_load >= p.n_chunks) { refilling = false; break; }
             }
         }
-        mbar_wait(&full[s], ph);
-        const uint32_t *dw = reinterpret_cast<const uint32_t *>(ring + s * STAGE_BYTES);
+        if constexpr (UDESC) {
+            if ((tid & 31) == 0) mbar_wait(&full[s], ph);
+            __syncwarp();
+        } else {
+            mbar_wait(&full[s], ph);
+        }
+        const uint32_t *dwp = reinterpret_cast<const uint32_t *>(ring + s * STAGE_BYTES);
+        uint32_t ubase = 0;
+        if constexpr (UDESC) ubase = up.off[c];
+        auto dw = [&](int idx) -> uint32_t {
+            if constexpr (UDESC) return up.w[ubase + idx];
+            else return dwp[idx];
+        };
         uint32_t cp = smem_u32(ring + s * STAGE_BYTES + MPX_DESC_WORDS * 4);
-        const int iend = MPX_DESC_HDR + (int)dw[0];
-        for (int i = MPX_DESC_HDR; i < iend;) {
+        const int iend = MPX_DESC_HDR + (int)dw(0);
+        // UDESC: records have a fixed size (no irregular ones, the plan checks), so the word index
+        // is a function of a plain loop counter
+        const int nrec = (iend - MPX_DESC_HDR) / (1 + NCW);
+        for (int rec = 0, i = MPX_DESC_HDR; UDESC ? rec < nrec : i < iend; ++rec) {
+            if constexpr (UDESC) i = MPX_DESC_HDR + rec * (1 + NCW);
             if (refilling) {
                 // thread 0, between records: hand a released stage straight back to the TMA
                 const int sp = next_load % S;
@@ -331,10 +355,10 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                     refilling = ++next_load < p.n_chunks;
                 }
             }
-            const uint32_t w = dw[i];
+            const uint32_t w = dw(i);
             uint32_t counts[NCW];
 #pragma unroll
-            for (int z = 0; z < NCW; ++z) counts[z] = dw[i + 1 + z];
+            for (int z = 0; z < NCW; ++z) counts[z] = dw(i + 1 + z);
             i += 1 + NCW;
             const int e1 = w & 255;
             const int nf = (w >> 8) & 15;
@@ -364,10 +388,10 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
             } else if (nf) {
                 // fold finished subtrees upwards: levels 0..nf-1 (dimensions 2..nf+1)
                 int adv = 1, cur = (w >> 14) & 255;
-                const bool irregular = (w & MPX_D_IRREG) != 0;
+                const bool irregular = !UDESC && (w & MPX_D_IRREG) != 0;
                 const bool last = (w & MPX_D_LAST) != 0;
                 if (irregular) {
-                    const uint32_t x = dw[i];
+                    const uint32_t x = dw(i);
                     cur = x & 255;
                     adv = (int)(x >> 8);
                 }
@@ -400,7 +424,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                 } else {
                     // dimension 2 is complete as well: hand its sum upwards and restart it
                     {
-                        const int st = irregular ? (int)dw[i + 1] : 0;
+                        const int st = irregular ? (int)dw(i + 1) : 0;
 #pragma unroll
                         for (int r = 0; r < R; ++r) {
                             low[r] = fma(t2[r], low[r], a2[r]);
@@ -425,7 +449,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                             tv[r] = ut[r * NT];
                             av[r] = ut[up_stride + r * NT];
                         }
-                        const int st = irregular ? (int)dw[i + 1 + u] : 0;
+                        const int st = irregular ? (int)dw(i + 1 + u) : 0;
 #pragma unroll
                         for (int r = 0; r < R; ++r) {
                             low[r] = fma(tv[r], low[r], av[r]);
@@ -477,7 +501,7 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
                         }
                     }
                 }
-                if (irregular) i += nf;
+                if (!UDESC && irregular) i += nf;
             }
         }
         mbar_arrive(&empty[s]);
@@ -495,6 +519,19 @@ __global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const EvalParams p)
     }
 }
 
+template <int L0P, int R, int A, int NT, int MINB, bool DERIV>
+__global__ void __launch_bounds__(NT, MINB) eval_tree_kernel(const __grid_constant__ EvalParams p)
+{
+    eval_tree_body<L0P, R, A, NT, DERIV, NoUniformProgram>(p, NoUniformProgram());
+}
+
+template <int L0P, int R, int A, int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
+eval_tree_kernel_u(const __grid_constant__ EvalParams p, const __grid_constant__ MpxUniformProgram up)
+{
+    eval_tree_body<L0P, R, A, NT, false, MpxUniformProgram>(p, up);
+}
+
 // (derivative evaluation builds the 128- and 64-thread variants only: half the code size)
 template <int L0P, int R, int A, int NT, int MINB, bool DERIV>
 const void *kfn_main()
@@ -506,7 +543,15 @@ const void *kfn_main()
 struct Variant {
     int l0p, r, nt;
     const void *fn;
+    const void *fn_u;     // the same kernel with the record stream as a kernel parameter, or null
 };
+
+template <int L0P, int R, int A, int NT, int MINB, bool DERIV>
+const void *kfn_u()
+{
+    if constexpr (DERIV) return nullptr;
+    else return reinterpret_cast<const void *>(&eval_tree_kernel_u<L0P, R, A, NT, MINB>);
+}
 
 template <int L0P, int R, int A, int NT, int MINB, bool DERIV>
 const void *kfn()
@@ -536,30 +581,30 @@ int tree_launch(mpx_plan *pl, MpxImage *img, const double *xx, int64_t P, int64_
     // kernel variants: (dimension-0 table size, points per thread, threads per CTA); for each
     // table size the first entry whose shared memory fits is taken
     static const Variant variants[] = {
-        {10, 4, 256, kfn_main<10, 4, 1, 256, 1, DERIV>()},
-        {10, 4, 128, kfn<10, 4, 1, 128, 1, DERIV>()},
-        {10, 4, 64, kfn<10, 4, 1, 64, 1, DERIV>()},
-        {10, 1, 64, kfn<10, 1, 2, 64, 1, DERIV>()},      // last resort: very long dimension-1 tables
-        {18, 4, 256, kfn_main<18, 4, 1, 256, 1, DERIV>()},
-        {18, 4, 128, kfn<18, 4, 1, 128, 1, DERIV>()},
-        {18, 4, 64, kfn<18, 4, 1, 64, 1, DERIV>()},
-        {18, 1, 64, kfn<18, 1, 2, 64, 1, DERIV>()},
-        {26, 3, 256, kfn_main<26, 3, 1, 256, 1, DERIV>()},
-        {26, 3, 128, kfn<26, 3, 1, 128, 1, DERIV>()},
-        {26, 3, 64, kfn<26, 3, 1, 64, 1, DERIV>()},
-        {26, 1, 64, kfn<26, 1, 2, 64, 1, DERIV>()},
-        {34, 2, 256, kfn_main<34, 2, 2, 256, 1, DERIV>()},
-        {34, 2, 128, kfn<34, 2, 2, 128, 1, DERIV>()},
-        {34, 2, 64, kfn<34, 2, 2, 64, 1, DERIV>()},
-        {34, 1, 64, kfn<34, 1, 2, 64, 1, DERIV>()},
-        {66, 1, 256, kfn_main<66, 1, 2, 256, 1, DERIV>()},
-        {66, 1, 128, kfn<66, 1, 2, 128, 1, DERIV>()},
-        {66, 1, 64, kfn<66, 1, 2, 64, 1, DERIV>()},
+        {10, 4, 256, kfn_main<10, 4, 1, 256, 1, DERIV>(), kfn_u<10, 4, 1, 256, 1, DERIV>()},
+        {10, 4, 128, kfn<10, 4, 1, 128, 1, DERIV>(), kfn_u<10, 4, 1, 128, 1, DERIV>()},
+        {10, 4, 64, kfn<10, 4, 1, 64, 1, DERIV>(), kfn_u<10, 4, 1, 64, 1, DERIV>()},
+        {10, 1, 64, kfn<10, 1, 2, 64, 1, DERIV>(), nullptr},      // last resort: very long dimension-1 tables
+        {18, 4, 256, kfn_main<18, 4, 1, 256, 1, DERIV>(), kfn_u<18, 4, 1, 256, 1, DERIV>()},
+        {18, 4, 128, kfn<18, 4, 1, 128, 1, DERIV>(), kfn_u<18, 4, 1, 128, 1, DERIV>()},
+        {18, 4, 64, kfn<18, 4, 1, 64, 1, DERIV>(), kfn_u<18, 4, 1, 64, 1, DERIV>()},
+        {18, 1, 64, kfn<18, 1, 2, 64, 1, DERIV>(), nullptr},
+        {26, 3, 256, kfn_main<26, 3, 1, 256, 1, DERIV>(), kfn_u<26, 3, 1, 256, 1, DERIV>()},
+        {26, 3, 128, kfn<26, 3, 1, 128, 1, DERIV>(), kfn_u<26, 3, 1, 128, 1, DERIV>()},
+        {26, 3, 64, kfn<26, 3, 1, 64, 1, DERIV>(), kfn_u<26, 3, 1, 64, 1, DERIV>()},
+        {26, 1, 64, kfn<26, 1, 2, 64, 1, DERIV>(), nullptr},
+        {34, 2, 256, kfn_main<34, 2, 2, 256, 1, DERIV>(), kfn_u<34, 2, 2, 256, 1, DERIV>()},
+        {34, 2, 128, kfn<34, 2, 2, 128, 1, DERIV>(), kfn_u<34, 2, 2, 128, 1, DERIV>()},
+        {34, 2, 64, kfn<34, 2, 2, 64, 1, DERIV>(), kfn_u<34, 2, 2, 64, 1, DERIV>()},
+        {34, 1, 64, kfn<34, 1, 2, 64, 1, DERIV>(), nullptr},
+        {66, 1, 256, kfn_main<66, 1, 2, 256, 1, DERIV>(), nullptr},
+        {66, 1, 128, kfn<66, 1, 2, 128, 1, DERIV>(), nullptr},
+        {66, 1, 64, kfn<66, 1, 2, 64, 1, DERIV>(), nullptr},
 #ifdef MPX_TUNING
         // measured and dropped; built only with -DMPX_TUNING, MPX_EVAL_VARIANT=<index>
-        {18, 4, 256, kfn_main<18, 4, 2, 256, 1, DERIV>()},   // 19: two accumulators per point
-        {18, 3, 384, kfn<18, 3, 1, 384, 1, DERIV>()},   // 20: 3 points, 12 warps
-        {18, 2, 512, kfn<18, 2, 1, 512, 1, DERIV>()},   // 21: 2 points, 16 warps in one CTA
+        {18, 4, 256, kfn_main<18, 4, 2, 256, 1, DERIV>(), kfn_u<18, 4, 2, 256, 1, DERIV>()},   // 19: two accumulators per point
+        {18, 3, 384, kfn<18, 3, 1, 384, 1, DERIV>(), nullptr},   // 20: 3 points, 12 warps
+        {18, 2, 512, kfn<18, 2, 1, 512, 1, DERIV>(), nullptr},   // 21: 2 points, 16 warps in one CTA
 #endif
     };
     constexpr int n_standard = 19;
@@ -637,6 +682,12 @@ int tree_launch(mpx_plan *pl, MpxImage *img, const double *xx, int64_t P, int64_
     if (tiles > 0x7fffffffLL || k > 65535)
         return mpx_fail(MPX_ERR_UNSUPPORTED, "too many points or polynomials for one launch");
     dim3 grid((unsigned)tiles, (unsigned)k, 1);
+    if (v->fn_u && !pl->uprog.empty() && mpx_test_eval_uniform != 2) {
+        MPX_CUDA(mpx_allow_max_smem(v->fn_u));
+        void *args[] = {(void *)&prm, (void *)pl->uprog.data()};
+        MPX_CUDA(cudaLaunchKernel(v->fn_u, grid, dim3(nt, 1, 1), args, smem, stream));
+        return mpx_image_release(img, stream);
+    }
     void *args[] = {(void *)&prm};
     MPX_CUDA(cudaLaunchKernel(v->fn, grid, dim3(nt, 1, 1), args, smem, stream));
     return mpx_image_release(img, stream);

@@ -567,6 +567,35 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
 
     if ((rc = upload(&pl->d_desc, pl->prog.desc)) != MPX_OK) return rc;
     if ((rc = upload(&pl->d_slot_src, pl->prog.slot_src)) != MPX_OK) return rc;
+    {
+        // the used record words as a kernel parameter (mpx_eval_kernel.cuh), if they fit and
+        // every record is regular: the uniform kernels index the stream by record number
+        const int nc = pl->prog.n_chunks;
+        size_t total = 0;
+        for (int c = 0; c < nc; ++c) total += MPX_DESC_HDR + pl->prog.desc[(size_t)c * MPX_DESC_WORDS];
+        bool regular = pl->tree_ok;
+        const int rec_words = 1 + mpx_count_words(mpx_l0p_for(pl->max_exp[0]));
+        for (int c = 0; c < nc && regular; ++c) {
+            const uint32_t *src = pl->prog.desc.data() + (size_t)c * MPX_DESC_WORDS;
+            if (src[0] % rec_words) regular = false;
+            for (uint32_t i = 0; i + rec_words <= src[0] && regular; i += rec_words)
+                if (src[MPX_DESC_HDR + i] & MPX_D_IRREG) regular = false;
+        }
+        if (regular && nc <= MPX_U_CHUNKS && total <= (size_t)MPX_U_WORDS) {
+            pl->uprog.resize(1);
+            MpxUniformProgram &u = pl->uprog[0];
+            memset(&u, 0, sizeof(u));
+            uint32_t at = 0;
+            for (int c = 0; c < nc; ++c) {
+                const uint32_t *src = pl->prog.desc.data() + (size_t)c * MPX_DESC_WORDS;
+                const uint32_t n = MPX_DESC_HDR + src[0];
+                u.off[c] = at;
+                std::copy(src, src + n, u.w + at);
+                at += n;
+            }
+            u.off[nc] = at;
+        }
+    }
     if (pl->tprog.usable) {
         if ((rc = upload(&pl->d_tdesc, pl->tprog.desc)) != MPX_OK) return rc;
         if ((rc = upload(&pl->d_tslot_src, pl->tprog.slot_src)) != MPX_OK) return rc;
