@@ -86,7 +86,6 @@ template <int L0P, int R, int A, int NT, int K, bool DERIV>
 __device__ __forceinline__ void run_leaves(double (&acc1)[R], const double (&T0)[R][L0P],
                                            uint32_t &cp, uint32_t &t1a, int cnt)
 {
-    const uint32_t cp_end = cp + (uint32_t)cnt * (16u * K);
 #pragma unroll 1
     do {
         double2 cf[K];
@@ -123,7 +122,7 @@ __device__ __forceinline__ void run_leaves(double (&acc1)[R], const double (&T0)
         }
         cp += 16 * K;
         t1a += T1Layout<R, NT>::ROW_BYTES;
-    } while (cp != cp_end);
+    } while (--cnt);
 }
 
 // walk the lengths of one record downwards: K = L0P/2, ..., 1
