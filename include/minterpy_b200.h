@@ -77,7 +77,7 @@ enum {
     MPX_INFO_TMMA_FMA = 11,    /* FMAs per point and polynomial of the tensor-core tree kernel
                                   (tile padding included), 0 if it was not built             */
     MPX_INFO_MMA_MIN_K = 12    /* smallest k evaluated by the many-polynomial tensor kernel
-                                  (4, 8 or 13, by leaf length; 1: every k; 0: never, m > 8)     */
+                                  (4, 8, 13, 27 or 33, by leaf length; 1: every k; 0: never, m > 8)     */
 };
 int mpx_plan_info(const mpx_plan *plan, int what, int64_t *value_out);
 
@@ -107,8 +107,7 @@ int mpx_eval(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
  *   - limit: the packed coefficients of one call must fit 8 MiB.  They take
  *     chunks * 1024 * k * 8 bytes for k below MPX_INFO_MMA_MIN_K (chunks = MPX_INFO_CHUNKS) and
  *     about 1.1 * N * k * 8 bytes (k rounded up to 8, 16, 32 or a multiple of 64) from there on:
- *     up to 32 polynomials per
- *     call at BASELINE config 2.  Beyond that the call returns MPX_ERR_UNSUPPORTED and does
+ *     up to 32 polynomials per call at BASELINE config 2.  Beyond that the call returns MPX_ERR_UNSUPPORTED and does
  *     nothing -- split k, or use mpx_eval.
  *   - the first call on a device looks the array's address up (set-up); make that first call
  *     before starting any stream capture, and before the application takes all device memory:

@@ -281,20 +281,26 @@ size_t mma_smem_bytes(const mpx_plan *pl, int nt8, int nw)
 }  // namespace
 
 
-// Smallest k that goes to this kernel when the tree kernel could take the plan as well.
-// Crossover against the tree kernel run once per polynomial (measured, 1e6 points): index sets
-// with long leaves (cfg2: 10 monomials per leaf, cfg4: 7) are faster on the tree kernel up to
-// k = 12 (cfg2 k = 8: 21 vs 32 ms, k = 12: 32 vs 43 ms; level at k = 16); sets with short leaves
-// (cfg3: 2.7) are record-bound there: k = 8 takes 26 vs 65 ms, and even k = 4, padded to the
-// 8-column tile here, 26 vs 33 ms.
+// Smallest k that goes to this kernel when a tree kernel could take the plan as well.
+// Crossover against the tree kernel run once per polynomial (measured in round 2 with the
+// uniform-control tree kernel, 1e6 points, tools/bench_k_sweep.py; this kernel costs the same for
+// every k of a tile size 8 / 16 / 32): cfg2 (10 monomials per leaf) 2.33 ms per polynomial against
+// 31.8 / 42.6 / 61.6 ms -- the tree kernel wins up to k = 26; cfg5 (33 per leaf, tensor-core tree
+// kernel) 2.98 ms against 41.8 / 54.9 / 114.9 -- up to k = 32 and beyond; cfg4 (7 per leaf) 7.3 ms
+// against 84 / 109 / 159 -- up to k = 12 (and 13, 14, 20 by a few per cent: ignored); cfg3 (2.7
+// per leaf) 3.3 ms against 13.4 / 16.4 / 21.1 -- level at k = 4, this kernel from there.
 int mpx_mma_min_k(const mpx_plan *pl)
 {
 #ifdef MPX_TUNING
     static const int env_min_k = getenv("MPX_EVAL_MMA_MIN_K") ? atoi(getenv("MPX_EVAL_MMA_MIN_K")) : 0;
     if (env_min_k > 0) return env_min_k;
 #endif
-    if (pl->tree_ok && pl->prog.n_leaves > 0 && pl->N >= 6 * pl->prog.n_leaves) return 13;
-    if (pl->tree_ok && pl->prog.n_leaves > 0 && pl->N < 4 * pl->prog.n_leaves) return 4;
+    if (pl->tree_ok && pl->prog.n_leaves > 0) {
+        if (pl->N >= 16 * pl->prog.n_leaves) return 33;
+        if (pl->N >= 8 * pl->prog.n_leaves) return 27;
+        if (pl->N >= 6 * pl->prog.n_leaves) return 13;
+        if (pl->N < 4 * pl->prog.n_leaves) return 4;
+    }
     return 8;
 }
 

@@ -624,11 +624,12 @@ def test_one_thread_per_gpu(mpb, golden_cfg):
 
 
 def test_kernel_choice_by_leaf_length(mpb, golden_cfg):
-    """MPX_INFO_MMA_MIN_K: long-leaf sets (cfg2, cfg4, cfg5) keep the tree kernel up to k = 12,
-    short-leaf sets (cfg3) go to the many-polynomial tensor kernel from k = 4; values on both
-    sides of each threshold agree with the oracle to the one tolerance."""
+    """MPX_INFO_MMA_MIN_K: the longer the leaves, the longer the tree kernel run once per
+    polynomial beats the many-polynomial tensor kernel (cfg5: up to k = 32, cfg2: 26, cfg4: 12);
+    short-leaf sets (cfg3) go to the tensor kernel from k = 4; values on both sides of each
+    threshold agree with the oracle to the one tolerance."""
     from minterpy_b200 import _lib
-    want = {"cfg2": 13, "cfg4": 13, "cfg5": 13, "cfg3": 4}
+    want = {"cfg2": 27, "cfg4": 13, "cfg5": 33, "cfg3": 4}
     rng = np.random.default_rng(31)
     for tag, min_k in want.items():
         g = golden_cfg(tag)

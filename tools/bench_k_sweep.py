@@ -20,7 +20,7 @@ tag=sys.argv[1]; P=int(sys.argv[2])
 g=golden_io.load(tag); e,gp=g['exponents'],g['generating_points']
 plan=mpb.get_plan(e,gp)
 xx=torch.rand((P,e.shape[1]),dtype=torch.float64,device='cuda')*2-1
-for k in (4,6,8,12,16,24,32,48):
+for k in (2,3,4,5,6,7,8,10,12,14,16,20,24):
     c=torch.rand((e.shape[0],k),dtype=torch.float64,device='cuda')
     out=torch.empty((P,k),dtype=torch.float64,device='cuda')
     for _ in range(2): plan._eval_torch(xx,c,out=out)
