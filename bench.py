@@ -588,7 +588,9 @@ def main():
                     "flops_per_point_model": model, "flops_per_point_executed": executed,
                     "fma_per_point": fma,
                     "kernel": ("eval_mma_kernel" if many_poly else
-                               "eval_tmma_kernel" if tensor_path else "eval_tree_kernel"),
+                               "eval_tmma_kernel" if tensor_path else
+                               "eval_tree_kernel_u" if plan.info(_lib.INFO_UNIFORM_PROGRAM) else
+                               "eval_tree_kernel"),
                     "kernel_ms": kernel_ms,
                     "hbm_gbs": P * 8 * (m + k) / (kernel_ms * 1e-3) / 1e9}
         # (rank 0 at N = 1 only: with N > 1 the driver's reference arm carries the CPU figure)

@@ -76,6 +76,8 @@ enum {
                                   2 = shared-memory-table tensor kernel (long dimension 0)   */
     MPX_INFO_TMMA_FMA = 11,    /* FMAs per point and polynomial of the tensor-core tree kernel
                                   (tile padding included), 0 if it was not built             */
+    MPX_INFO_UNIFORM_PROGRAM = 13, /* 1 if the tree kernel takes its record stream as a kernel
+                                  parameter (uniform control flow; regular index sets)        */
     MPX_INFO_MMA_MIN_K = 12    /* smallest k evaluated by the many-polynomial tensor kernel
                                   (4, 8, 13, 27 or 33, by leaf length; 1: every k; 0: never, m > 8)     */
 };

@@ -53,7 +53,7 @@ MPX_DENSE_LOWER = 1
 MPX_OK, MPX_ERR_ARG, MPX_ERR_INCOMPLETE, MPX_ERR_CUDA, MPX_ERR_UNSUPPORTED, MPX_ERR_NOMEM = range(6)
 (INFO_N, INFO_M, INFO_COMPLETE, INFO_EVAL_FMA, INFO_DDS_UPDATES, INFO_LEAVES, INFO_DEVICE,
  INFO_SCRATCH_BYTES, INFO_EVAL_OTHER_FP64, INFO_CHUNKS, INFO_SMALLK_KERNEL,
- INFO_TMMA_FMA, INFO_MMA_MIN_K) = range(13)
+ INFO_TMMA_FMA, INFO_MMA_MIN_K, INFO_UNIFORM_PROGRAM) = range(14)
 
 _lib = None
 

@@ -796,6 +796,7 @@ extern "C" int mpx_plan_info(const mpx_plan *pl, int what, int64_t *value_out)
         *value_out = mpx_tmma_eligible(pl, 1) ? 1 : (pl->tree_ok ? 0 : 2);
         break;
     case MPX_INFO_TMMA_FMA: *value_out = pl->tprog.fma_per_point; break;
+    case MPX_INFO_UNIFORM_PROGRAM: *value_out = pl->uprog.empty() ? 0 : 1; break;
     case MPX_INFO_MMA_MIN_K:
         *value_out = (pl->m <= 8 && pl->d_exp64) ? (pl->tree_ok ? mpx_mma_min_k(pl) : 1) : 0;
         break;
