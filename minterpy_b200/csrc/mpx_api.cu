@@ -160,13 +160,9 @@ public:
     // run fn(part) for part = 0..parts-1 on the helpers and the calling thread
     void run(int parts, const std::function<void(int)> &fn)
     {
-        // the pool is busy with another caller's block (several GPUs fed from one process):
-        // this thread copies its block alone rather than queue behind it
-        std::unique_lock<std::mutex> one_job(gate, std::try_to_lock);
-        if (!one_job.owns_lock()) {
-            for (int p = 0; p < parts; ++p) fn(p);
-            return;
-        }
+        // one job at a time: callers feeding several GPUs from one process queue here (letting a
+        // second caller copy its block alone instead was measured: 103 against 85 ms at 8 GPUs)
+        std::lock_guard<std::mutex> one_job(gate);
         {
             std::lock_guard<std::mutex> lk(mu);
             job = &fn;
