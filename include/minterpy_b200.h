@@ -160,8 +160,8 @@ int mpx_dds_host(mpx_plan *plan, const double *in_h, int k, int64_t ld_in, doubl
  * Dense operator apply out = T @ c.
  *   replaces: MatrixOperator.__matmul__  src/minterpy/schemes/matrix_operator.py:13-22
  * T (rows x cols, ld_t), c (cols x k, ld_c), out (rows x k, ld_out), all device, float64.
- * Up to 8 coefficient columns run as FMA dot products, more as one pass over T per 32 columns
- * on the FP64 tensor cores; T is read once per pass and that read bounds the call.
+ * One or two coefficient columns run as FMA dot products, more as one pass over T per 32
+ * columns on the FP64 tensor cores; T is read once per pass and that read bounds the call.
  */
 int mpx_apply_dense(int device, const double *T, int64_t rows, int64_t cols, int64_t ld_t,
                     const double *c, int k, int64_t ld_c, double *out, int64_t ld_out,

@@ -5,7 +5,9 @@
 // 32 rows; a warp owns 4 of them and sweeps the columns, each lane keeping KT partial sums per
 // row, reduced by shuffles at the end.  The coefficient rows a span of columns needs are staged
 // transposed in shared memory by the whole CTA (one barrier per 64 KB of matrix), so the inner
-// loop reads them with conflict-free 16-byte loads whatever k and ld_c are.
+// loop reads them with conflict-free 16-byte loads whatever k and ld_c are.  Round 2: this FMA
+// form serves one or two coefficient columns; from three on the tensor-core kernel below reads T
+// once for up to 32 columns (k = 8: 1.07 ms against 1.55 ms here at N = 24 809).
 #include "mpx_common.h"
 
 namespace {
@@ -24,12 +26,13 @@ constexpr int CS = SPAN + 4;      // pitch of a staged coefficient row (two colu
 // hence its rows 0 and 2 are aligned and rows 1 and 3 are not: those load their pairs one
 // column further right (columns j+1, j+2 instead of j, j+1), their column 0 is added by lane 0.
 // KT = coefficient columns per pass (grid.y covers k in steps of KT).
-template <bool ODD, int KT>
+template <bool ODD, int KT, bool LOWER>
 __global__ void __launch_bounds__(NTHREADS)
 dense_apply_kernel(const double *__restrict__ T, int64_t rows, int64_t cols_all, int64_t ld_t,
                    const double *__restrict__ c, int k, int64_t ld_c, double *__restrict__ out,
-                   int64_t ld_out, int lower)
+                   int64_t ld_out)
 {
+    constexpr bool lower = LOWER;
     __shared__ __align__(16) double cs[2][KT][CS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // lower-triangular operator: the heavy row blocks (bottom of the matrix) are scheduled
@@ -212,10 +215,14 @@ void launch_vec(bool odd, dim3 grid, cudaStream_t st, const double *T, int64_t r
                 int64_t ld_t, const double *c, int k, int64_t ld_c, double *out, int64_t ld_out,
                 int lower)
 {
-    if (odd)
-        dense_apply_kernel<true, KT><<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower);
+    if (odd && lower)
+        dense_apply_kernel<true, KT, true><<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out);
+    else if (odd)
+        dense_apply_kernel<true, KT, false><<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out);
+    else if (lower)
+        dense_apply_kernel<false, KT, true><<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out);
     else
-        dense_apply_kernel<false, KT><<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower);
+        dense_apply_kernel<false, KT, false><<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out);
 }
 
 // ---- many coefficient columns: one pass over T on the FP64 tensor cores ------------------------
@@ -364,11 +371,12 @@ extern "C" int mpx_apply_dense_ex(int device, const double *T, int64_t rows, int
     if (!dg.ok) return mpx_fail(MPX_ERR_CUDA, "cannot select CUDA device");
     const int lower = (flags & MPX_DENSE_LOWER) ? 1 : 0;
     cudaStream_t st = (cudaStream_t)stream;
-    if (k > 8) {
-        // one pass over T for up to 32 columns on the tensor cores (16 per pass up to k = 16:
-        // smaller tiles, more CTAs per SM)
-        int rc = k <= 16 ? launch_mma<2>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower, st)
-                         : launch_mma<4>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower, st);
+    if (k > 2) {
+        // one pass over T for up to 32 columns on the tensor cores (8 or 16 per pass up to
+        // k = 16: smaller tiles, more CTAs per SM)
+        int rc = k <= 8    ? launch_mma<1>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower, st)
+                 : k <= 16 ? launch_mma<2>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower, st)
+                           : launch_mma<4>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower, st);
         if (rc != MPX_OK) return rc;
         MPX_CUDA(cudaGetLastError());
         return MPX_OK;
@@ -381,14 +389,9 @@ extern "C" int mpx_apply_dense_ex(int device, const double *T, int64_t rows, int
         dense_apply_plain_kernel<<<grid, NTHREADS, 0, st>>>(T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower);
     } else {
         const bool odd = (ld_t & 1) != 0;
-        const int kt = k >= 8 ? 8 : k >= 3 ? 4 : k;          // coefficient columns per pass
-        dim3 grid(gx, (unsigned)((k + kt - 1) / kt), 1);
-        switch (kt) {
-        case 1: launch_vec<1>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower); break;
-        case 2: launch_vec<2>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower); break;
-        case 4: launch_vec<4>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower); break;
-        default: launch_vec<8>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower); break;
-        }
+        dim3 grid(gx, 1, 1);                                 // k = 1 or 2: one pass
+        if (k == 1) launch_vec<1>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower);
+        else launch_vec<2>(odd, grid, st, T, rows, cols, ld_t, c, k, ld_c, out, ld_out, lower);
     }
     MPX_CUDA(cudaGetLastError());
     return MPX_OK;
