@@ -293,3 +293,43 @@ def test_dds_kernels_agree_bit_for_bit_on_ragged_widths_and_special_values(mpb, 
             assert _same_bits(got, want), (tag, k)
             if not special:
                 assert np.array_equal(got[:, :2], oracle.dds(np.ascontiguousarray(vals[:, :2]), e, gp)), (tag, k)
+
+
+def test_uniform_control_tree_kernel_is_bit_identical_to_the_ring_kernel(mpb, golden_cfg, golden_small):
+    """Index sets without irregular records run the tree kernel that takes its record stream as a
+    kernel parameter (uniform control flow, csrc/mpx_eval_kernel.cuh); a test hook sends the same
+    plan through the ring-fed kernel.  Same arithmetic per point: identical bits, on every golden
+    shape, for several polynomials, ragged point counts, and with the tensor-core tree kernel
+    switched off so that the DFMA kernels are what runs."""
+    import torch
+    from minterpy_b200 import _lib
+    lib = _lib.lib()
+    shapes = [(t, golden_small[f"{t}/exponents"], golden_small[f"{t}/generating_points"])
+              for t in sorted({k.split("/")[0] for k in golden_small})]
+    for tag in ("cfg1", "cfg2", "cfg3", "cfg4", "cfg5"):
+        g = golden_cfg(tag)
+        shapes.append((tag, g["exponents"], g["generating_points"]))
+    extra = golden_io.load("shapes_extra")
+    for t in sorted({k.split("/")[0] for k in extra}):
+        shapes.append((t, extra[f"{t}/exponents"], extra[f"{t}/generating_points"]))
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    used = 0
+    lib.mpx_debug_set_tmma(2)
+    try:
+        for tag, e, gp in shapes:
+            N, m = e.shape
+            plan = mpb.Plan(e, gp)
+            used += plan.info(_lib.INFO_UNIFORM_PROGRAM)
+            for P, k in ((1, 1), (777, 3), (40_001, 2)):
+                xx = torch.rand((P, m), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+                c = torch.rand((N, k), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+                a = plan.eval(xx, c)
+                lib.mpx_debug_set_eval_uniform(2)
+                try:
+                    b = plan.eval(xx, c)
+                finally:
+                    lib.mpx_debug_set_eval_uniform(0)
+                assert torch.equal(a, b), (tag, P, k)
+    finally:
+        lib.mpx_debug_set_tmma(0)
+    assert used >= len(shapes) - 2          # complete index sets are regular: nearly all qualify
