@@ -470,12 +470,9 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     double2 *dy2 = reinterpret_cast<double2 *>(fsm);                  // (divisor, reciprocal), L x L
     // flag words behind the fiber buffers and the barriers: bit r of word l = entry (l, r) flagged
     unsigned long long *fm = reinterpret_cast<unsigned long long *>(dy2 + L * L + (size_t)FW * L * H * 32) + FW;
-    for (int i = threadIdx.x; i < L * L; i += blockDim.x) dy2[i] = reinterpret_cast<const double2 *>(dy)[i];
-    for (int i = threadIdx.x; i < L; i += blockDim.x) fm[i] = fmask[i];
-    __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int f = blockIdx.x * FW + warp;
-    if (f >= n_work) return;
+    const bool valid = f < n_work;             // (a warp without a fiber still stages the table)
     constexpr int C = 2 * H;
     const int64_t col0 = (int64_t)blockIdx.y * (32 * C) + 2 * lane;      // pair h starts at col0 + 64 h
     // pairs of this lane that exist (k may end inside the warp's column block); a lane without
@@ -483,8 +480,8 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     unsigned active = 0;
 #pragma unroll
     for (int h = 0; h < H; ++h) active |= (col0 + 64 * h < k) ? 1u << h : 0u;
-    const int o = woff[f];
-    const int len = woff[f + 1] - o;
+    const int o = valid ? woff[f] : 0;
+    const int len = valid ? woff[f + 1] - o : 0;
     const int32_t *rows = wrows + o;
     double2 *bw = dy2 + L * L + (size_t)warp * L * H * 32;               // this warp's fiber buffer
     double2 *bl = bw + lane;                                             // this lane's slots
@@ -506,9 +503,16 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
             for (int h = 0; h < H; ++h) bl[(r * H + h) * 32] = make_double2(0.0, 0.0);
     if (ncols < 32 * C) fence_proxy_async_smem();
     __syncwarp();
-    if (lane == 0) mbar_arrive_expect_tx(bar, row_bytes * (uint32_t)len);
-    for (int r = lane; r < len; r += 32)
-        bulk_g2s(bw + (size_t)r * H * 32, vals + (int64_t)rows[r] * ld + cw0, row_bytes, bar);
+    if (valid) {
+        if (lane == 0) mbar_arrive_expect_tx(bar, row_bytes * (uint32_t)len);
+        for (int r = lane; r < len; r += 32)
+            bulk_g2s(bw + (size_t)r * H * 32, vals + (int64_t)rows[r] * ld + cw0, row_bytes, bar);
+    }
+    // the tables are staged while the rows are on their way
+    for (int i = threadIdx.x; i < L * L; i += blockDim.x) dy2[i] = reinterpret_cast<const double2 *>(dy)[i];
+    for (int i = threadIdx.x; i < L; i += blockDim.x) fm[i] = fmask[i];
+    __syncthreads();
+    if (!valid) return;
     mbar_wait(bar, 0);
     bool bad = false;
     // Row-blocked sweep (see dds_fiber_kernel): element r receives its updates i = 1..r in order,
