@@ -333,3 +333,50 @@ def test_uniform_control_tree_kernel_is_bit_identical_to_the_ring_kernel(mpb, go
     finally:
         lib.mpx_debug_set_tmma(0)
     assert used >= len(shapes) - 2          # complete index sets are regular: nearly all qualify
+
+
+def _random_complete_set(mpb, rng):
+    """A downward-closed index set in the reference's ordering: an l_p set cut by per-dimension
+    caps (rows are dropped, never reordered, so the lexicographic order of core/utils.py:44-92
+    is kept)."""
+    from minterpy_b200 import generators
+    m = int(rng.integers(1, 7))
+    n = int(rng.integers(1, {1: 60, 2: 40, 3: 20, 4: 12, 5: 8, 6: 6}[m]))
+    lp = float(rng.choice([0.5, 1.0, 2.0, 3.0, np.inf]))
+    e = generators.get_exponent_matrix(m, n, lp)
+    caps = rng.integers(0, n + 1, m)
+    caps[int(rng.integers(0, m))] = n
+    e = np.ascontiguousarray(e[np.all(e <= caps, axis=1)])
+    rows = int(e.max()) + 2
+    gp = rng.uniform(-1, 1, (rows, m))
+    # distinct values per column, as a grid needs them
+    gp += np.arange(rows)[:, None] * 1e-3
+    return e, gp
+
+
+def test_seeded_sweep_of_complete_sets_against_the_oracle(mpb):
+    """40 seeded downward-closed sets (m = 1..6, l_p cut by caps, random generating points):
+    evaluation on every kernel the polynomial count selects, divided differences bit for bit at
+    widths on both sides of the column-kernel threshold, and one derivative each."""
+    rng = np.random.default_rng(20261107)
+    for trial in range(40):
+        e, gp = _random_complete_set(mpb, rng)
+        N, m = e.shape
+        plan = mpb.Plan(e, gp)
+        assert plan.is_complete
+        P = int(rng.integers(1, 700))
+        xx = rng.uniform(-1, 1, (P, m))
+        for k in (1, int(rng.integers(2, 9)), int(rng.integers(9, 80))):
+            c = rng.uniform(-1, 1, (N, k))
+            ref = oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=4)
+            assert rel_err(plan.eval(xx, c).reshape(P, k), ref.reshape(P, k)) <= EVAL_RTOL, (trial, e.shape, k)
+        for k in (1, int(rng.integers(2, 64)), 64 + 2 * int(rng.integers(0, 40)), 129):
+            v = rng.uniform(-1, 1, (N, k))
+            assert np.array_equal(plan.dds(v), oracle.dds(v, e, gp)), (trial, e.shape, k)
+        orders = rng.integers(0, 3, m)
+        k = int(rng.choice([1, 2, 11]))
+        c = rng.uniform(-1, 1, (N, k))
+        ref = oracle.deriv_newt_eval(xx, c, e, gp, orders)
+        got = plan.eval_deriv(xx, c, orders)
+        scale = max(np.max(np.abs(ref)), 1e-300)
+        assert np.max(np.abs(np.asarray(got).reshape(P, k) - ref.reshape(P, k))) <= 1e-12 * scale, (trial, e.shape, orders)
