@@ -215,24 +215,31 @@ int mpx_fail(int code, const std::string &msg);
 // to the size of one launch.  The attribute belongs to the function, process-wide, so two host
 // threads launching the same kernel with different sizes (two plans) would otherwise race: one
 // lowers the limit between the other's set and launch.
+// Done once per (kernel, device): the three runtime calls cost ~2 us of every launch otherwise.
+bool mpx_smem_raised(const void *fn, int device, bool mark);       // mpx_plan.cu
 template <typename F>
 inline cudaError_t mpx_allow_max_smem(F fn)
 {
     int device = 0, smem_max = 0;
     cudaError_t e = cudaGetDevice(&device);            // the entry points select the plan's device
     if (e != cudaSuccess) return e;
+    if (mpx_smem_raised(reinterpret_cast<const void *>(fn), device, false)) return cudaSuccess;
     e = cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+    e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+    if (e == cudaSuccess) mpx_smem_raised(reinterpret_cast<const void *>(fn), device, true);
+    return e;
 }
 
 struct DeviceGuard {
     int prev = -1;
-    bool ok = false;
+    bool ok = false, changed = false;
     explicit DeviceGuard(int dev) {
-        if (cudaGetDevice(&prev) == cudaSuccess && cudaSetDevice(dev) == cudaSuccess) ok = true;
+        if (cudaGetDevice(&prev) != cudaSuccess) return;
+        if (prev == dev) { ok = true; return; }          // the usual case: nothing to switch
+        if (cudaSetDevice(dev) == cudaSuccess) ok = changed = true;
     }
-    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    ~DeviceGuard() { if (changed) cudaSetDevice(prev); }
 };
 
 // kernels' host launchers (defined in the .cu files) ---------------------------------------

@@ -8,6 +8,8 @@
 #include <cstring>
 #include <memory>
 #include <numeric>
+#include <set>
+#include <utility>
 
 #include "mpx_common.h"
 
@@ -573,7 +575,8 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
         const int nc = pl->prog.n_chunks;
         size_t total = 0;
         for (int c = 0; c < nc; ++c) total += MPX_DESC_HDR + pl->prog.desc[(size_t)c * MPX_DESC_WORDS];
-        bool regular = pl->tree_ok;
+        // (no uniform-control instantiation exists for one point per thread: tables of 65 entries)
+        bool regular = pl->tree_ok && mpx_l0p_for(pl->max_exp[0]) < 66;
         const int rec_words = 1 + mpx_count_words(mpx_l0p_for(pl->max_exp[0]));
         for (int c = 0; c < nc && regular; ++c) {
             const uint32_t *src = pl->prog.desc.data() + (size_t)c * MPX_DESC_WORDS;
@@ -803,6 +806,18 @@ extern "C" int mpx_plan_info(const mpx_plan *pl, int what, int64_t *value_out)
     default: return mpx_fail(MPX_ERR_ARG, "unknown info key");
     }
     return MPX_OK;
+}
+
+bool mpx_smem_raised(const void *fn, int device, bool mark)
+{
+    static std::mutex mu;
+    static std::set<std::pair<const void *, int>> done;
+    std::lock_guard<std::mutex> lk(mu);
+    if (mark) {
+        done.insert({fn, device});
+        return true;
+    }
+    return done.count({fn, device}) != 0;
 }
 
 int mpx_image_acquire(MpxImage *img, size_t bytes, cudaStream_t stream)
