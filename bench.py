@@ -577,6 +577,7 @@ def main():
         except (OSError, ValueError, KeyError):
             traffic = None
         achieved = algo * P / (kernel_ms * 1e-3) / 1e12
+        horner = (not many_poly) and plan.info(_lib.INFO_SMALLK_KERNEL) == 3
         roofline = {"bound": "tensor" if tensor_path else "fp64", "achieved": achieved,
                     "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                     "algorithmic_bytes": P * 8 * (m + k),
@@ -588,6 +589,7 @@ def main():
                     "flops_per_point_model": model, "flops_per_point_executed": executed,
                     "fma_per_point": fma,
                     "kernel": ("eval_mma_kernel" if many_poly else
+                               "horner1d_kernel" if horner else
                                "eval_tmma_kernel" if tensor_path else
                                "eval_tree_kernel_u" if plan.info(_lib.INFO_UNIFORM_PROGRAM) else
                                "eval_tree_kernel"),

@@ -73,13 +73,14 @@ enum {
     MPX_INFO_EVAL_OTHER_FP64 = 8, /* FP64 adds/multiplies besides the FMAs, per point        */
     MPX_INFO_CHUNKS = 9,       /* chunks of the evaluation program                           */
     MPX_INFO_SMALLK_KERNEL = 10, /* kernel for k below MPX_INFO_MMA_MIN_K: 0 = DFMA tree, 1 = tensor-core tree,
-                                  2 = shared-memory-table tensor kernel (long dimension 0)   */
+                                  2 = shared-memory-table tensor kernel (long dimension 0),
+                                  3 = Horner's rule (m = 1, any k)                           */
     MPX_INFO_TMMA_FMA = 11,    /* FMAs per point and polynomial of the tensor-core tree kernel
                                   (tile padding included), 0 if it was not built             */
     MPX_INFO_UNIFORM_PROGRAM = 13, /* 1 if the tree kernel takes its record stream as a kernel
                                   parameter (uniform control flow; regular index sets)        */
     MPX_INFO_MMA_MIN_K = 12    /* smallest k evaluated by the many-polynomial tensor kernel
-                                  (4, 8, 13, 27 or 33, by leaf length; 1: every k; 0: never, m > 8)     */
+                                  (4, 8, 13, 27 or 33, by leaf length; 1: every k; 0: never, m > 8 or m = 1) */
 };
 int mpx_plan_info(const mpx_plan *plan, int what, int64_t *value_out);
 

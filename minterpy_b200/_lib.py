@@ -47,6 +47,7 @@ DEBUG_SIGNATURES = {
     "mpx_debug_set_dds_group": (None, [c_int]),     # dds through the fused slice kernel
     "mpx_debug_set_eval_stages": (None, [c_int]),   # ring depth of the tree kernel (0 = default)
     "mpx_debug_set_eval_uniform": (None, [c_int]),  # 2: record stream from the ring, never as a parameter
+    "mpx_debug_set_eval_1d": (None, [c_int]),       # 2: m = 1 on the tree kernel, never Horner's rule
 }
 
 MPX_DENSE_LOWER = 1

@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libminterpy_b200.so")
-SOURCES = ["mpx_plan.cu", "mpx_eval.cu", "mpx_eval_deriv.cu", "mpx_eval_mma.cu", "mpx_eval_tmma.cu", "mpx_dds.cu", "mpx_monomials.cu", "mpx_dense.cu",
+SOURCES = ["mpx_plan.cu", "mpx_eval.cu", "mpx_eval_deriv.cu", "mpx_eval_1d.cu", "mpx_eval_mma.cu", "mpx_eval_tmma.cu", "mpx_dds.cu", "mpx_monomials.cu", "mpx_dense.cu",
            "mpx_api.cu", "mpx_noalloc.cu", "mpx_index.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--fmad=true"]

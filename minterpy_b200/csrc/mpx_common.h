@@ -170,6 +170,7 @@ struct mpx_plan {
     int32_t *d_tslot_src = nullptr;
     uint32_t *d_desc = nullptr;
     int32_t *d_slot_src = nullptr;
+    int32_t *d_row1d = nullptr;      // m = 1, distinct exponents: row of the monomial with exponent e, or -1
     double *d_gp = nullptr;          // (m x gp_rows) dimension-major copy of the generating points
     uint8_t *d_exp8 = nullptr;       // (N x m) exponents as bytes, for the monomial kernel
     int *d_max_exp = nullptr;        // (m) largest exponent per dimension
@@ -266,6 +267,12 @@ int mpx_launch_eval_mma(mpx_plan *plan, MpxImage *img, const double *xx, int64_t
                         cudaStream_t stream, const int *orders_h = nullptr);
 bool mpx_mma_fits(const mpx_plan *plan, int k);   // the tables of this index set fit shared memory
 // tensor-core tree kernel (complete sets, few polynomials), mpx_eval_tmma.cu
+// one-dimensional polynomials by Horner's rule (mpx_eval_1d.cu)
+bool mpx_1d_eligible(const mpx_plan *plan, int k);
+size_t mpx_1d_scratch_bytes(const mpx_plan *plan, int k);
+int mpx_launch_eval_1d(mpx_plan *plan, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,
+                       const double *coeffs, int k, int64_t ld_c, double *out, int64_t ld_out,
+                       cudaStream_t stream);
 bool mpx_tmma_eligible(const mpx_plan *plan, int k);
 size_t mpx_tmma_scratch_bytes(const mpx_plan *plan, int k);
 int mpx_launch_eval_tmma(mpx_plan *plan, MpxImage *img, const double *xx, int64_t P, int64_t ld_xx,

@@ -25,6 +25,8 @@ int mpx_launch_eval(mpx_plan *pl, MpxImage *img, const double *xx, int64_t P, in
                     cudaStream_t stream)
 {
     if (P == 0 && coeffs == nullptr) return MPX_OK;
+    if (mpx_1d_eligible(pl, k))
+        return mpx_launch_eval_1d(pl, img, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
     if (mpx_mma_eligible(pl, k))
         return mpx_launch_eval_mma(pl, img, xx, P, ld_xx, coeffs, k, ld_c, out, ld_out, stream);
     if (mpx_tmma_eligible(pl, k))
@@ -46,6 +48,7 @@ extern "C" void mpx_debug_set_eval_uniform(int mode) { mpx_test_eval_uniform = m
 
 size_t mpx_eval_scratch_bytes(const mpx_plan *pl, int k)
 {
+    if (mpx_1d_eligible(pl, k)) return mpx_1d_scratch_bytes(pl, k);
     if (mpx_mma_eligible(pl, k)) return mpx_mma_scratch_bytes(pl, k);
     if (mpx_tmma_eligible(pl, k)) return mpx_tmma_scratch_bytes(pl, k);
     return (size_t)pl->prog.n_chunks * MPX_COEF_CAP * (size_t)k * sizeof(double);

@@ -607,6 +607,18 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
     for (int i = 0; i < m; ++i)
         for (int j = 0; j < pl->gp_rows; ++j) gpt[(size_t)i * pl->gp_rows + j] = gp_h[(size_t)j * m + i];
     if ((rc = upload(&pl->d_gp, gpt)) != MPX_OK) return rc;
+    if (m == 1) {
+        // Horner kernel (mpx_eval_1d.cu): where each exponent's coefficient sits; duplicates
+        // (the reference would add them up) leave the plan on the tree kernel
+        std::vector<int32_t> row((size_t)pl->max_exp[0] + 1, -1);
+        bool distinct = N <= 0x7fffffffLL;
+        for (int64_t j = 0; j < N && distinct; ++j) {
+            int32_t &slot = row[(size_t)e[j]];
+            if (slot >= 0) distinct = false;
+            slot = (int32_t)j;
+        }
+        if (distinct && (rc = upload(&pl->d_row1d, row)) != MPX_OK) return rc;
+    }
     std::vector<uint8_t> e8((size_t)N * m);
     for (size_t t = 0; t < e8.size(); ++t) e8[t] = (uint8_t)e[t];
     if ((rc = upload(&pl->d_exp8, e8)) != MPX_OK) return rc;
@@ -734,6 +746,7 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
     DeviceGuard dg(pl->device);
     cudaFree(pl->d_desc);
     cudaFree(pl->d_slot_src);
+    cudaFree(pl->d_row1d);
     cudaFree(pl->d_tdesc);
     cudaFree(pl->d_tslot_src);
     cudaFree(pl->d_gp);
@@ -788,20 +801,23 @@ extern "C" int mpx_plan_info(const mpx_plan *pl, int what, int64_t *value_out)
     case MPX_INFO_N: *value_out = pl->N; break;
     case MPX_INFO_M: *value_out = pl->m; break;
     case MPX_INFO_COMPLETE: *value_out = pl->complete ? 1 : 0; break;
-    case MPX_INFO_EVAL_FMA: *value_out = pl->prog.fma_per_point; break;
-    case MPX_INFO_EVAL_OTHER_FP64: *value_out = pl->prog.other_fp64_per_point; break;
+    // (Horner kernel, m = 1: one FMA and one subtraction per exponent up to the largest)
+    case MPX_INFO_EVAL_FMA: *value_out = mpx_1d_eligible(pl, 1) ? pl->max_exp[0] : pl->prog.fma_per_point; break;
+    case MPX_INFO_EVAL_OTHER_FP64:
+        *value_out = mpx_1d_eligible(pl, 1) ? pl->max_exp[0] : pl->prog.other_fp64_per_point;
+        break;
     case MPX_INFO_DDS_UPDATES: *value_out = pl->dds_updates; break;
     case MPX_INFO_LEAVES: *value_out = pl->prog.n_leaves; break;
     case MPX_INFO_DEVICE: *value_out = pl->device; break;
     case MPX_INFO_SCRATCH_BYTES: *value_out = (int64_t)pl->image.bytes; break;
     case MPX_INFO_CHUNKS: *value_out = pl->prog.n_chunks; break;
     case MPX_INFO_SMALLK_KERNEL:
-        *value_out = mpx_tmma_eligible(pl, 1) ? 1 : (pl->tree_ok ? 0 : 2);
+        *value_out = mpx_1d_eligible(pl, 1) ? 3 : mpx_tmma_eligible(pl, 1) ? 1 : (pl->tree_ok ? 0 : 2);
         break;
     case MPX_INFO_TMMA_FMA: *value_out = pl->tprog.fma_per_point; break;
     case MPX_INFO_UNIFORM_PROGRAM: *value_out = pl->uprog.empty() ? 0 : 1; break;
     case MPX_INFO_MMA_MIN_K:
-        *value_out = (pl->m <= 8 && pl->d_exp64) ? (pl->tree_ok ? mpx_mma_min_k(pl) : 1) : 0;
+        *value_out = mpx_1d_eligible(pl, 1) ? 0 : (pl->m <= 8 && pl->d_exp64) ? (pl->tree_ok ? mpx_mma_min_k(pl) : 1) : 0;
         break;
     default: return mpx_fail(MPX_ERR_ARG, "unknown info key");
     }

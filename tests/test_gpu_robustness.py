@@ -380,3 +380,58 @@ def test_seeded_sweep_of_complete_sets_against_the_oracle(mpb):
         got = plan.eval_deriv(xx, c, orders)
         scale = max(np.max(np.abs(ref)), 1e-300)
         assert np.max(np.abs(np.asarray(got).reshape(P, k) - ref.reshape(P, k))) <= 1e-12 * scale, (trial, e.shape, orders)
+
+
+def test_one_dimensional_polynomials_by_horner_rule(mpb):
+    """m = 1 runs on the Horner kernel (mpx_eval_1d.cu) for any number of polynomials: against the
+    oracle and against the tree kernel (test hook) on dense, gappy and unsorted exponent lists,
+    ragged point counts, strided inputs, degrees beyond the tree kernel's 64, and duplicates
+    (which must stay on the tree kernel)."""
+    import torch
+    from minterpy_b200 import _lib
+    rng = np.random.default_rng(64)
+    cases = [np.arange(65), np.arange(1), np.arange(2), np.array([0, 2, 5, 9]), np.array([7, 0, 3, 64, 12]),
+             np.arange(200), np.array([255, 0, 100])]
+    for ex in cases:
+        e = ex.reshape(-1, 1).astype(np.int64)
+        gp = np.sort(rng.uniform(-1, 1, (int(e.max()) + 2, 1)), axis=0)[::-1].copy()
+        plan = mpb.Plan(e, gp)
+        assert plan.info(_lib.INFO_SMALLK_KERNEL) == 3
+        for k in (1, 2, 3, 4, 5, 32, 33):
+            for P in (1, 255, 2049, 70001):
+                xx = rng.uniform(-1, 1, (P, 1))
+                c = rng.uniform(-1, 1, (e.shape[0], k))
+                ref = oracle.eval_newton_polynomials(xx, c, e, gp, nthreads=4).reshape(P, k)
+                assert rel_err(plan.eval(xx, c).reshape(P, k), ref) <= EVAL_RTOL, (ex[:4], k, P)
+        # strided device tensors: the points are one column of a wider array, the coefficients
+        # and the result slices of wider ones
+        P, k = 5000, 3
+        wide = torch.rand((P, 4), dtype=torch.float64, device="cuda") * 2 - 1
+        cw = torch.rand((e.shape[0], 8), dtype=torch.float64, device="cuda")
+        ow = torch.zeros((P, 6), dtype=torch.float64, device="cuda")
+        got = plan._eval_torch(wide[:, 2:3], cw[:, 1:1 + k], out=ow[:, 2:2 + k])
+        ref = oracle.eval_newton_polynomials(wide[:, 2:3].cpu().numpy().copy(), cw[:, 1:1 + k].cpu().numpy().copy(), e, gp)
+        assert rel_err(got.cpu().numpy(), ref.reshape(P, k)) <= EVAL_RTOL
+        assert float(ow[:, :2].abs().max()) == 0.0 and float(ow[:, 5:].abs().max()) == 0.0
+    # the tree kernel on the same inputs (what m = 1 ran on before): within rounding of Horner
+    e = np.arange(65).reshape(-1, 1).astype(np.int64)
+    gp = rng.uniform(-1, 1, (65, 1))
+    xx = rng.uniform(-1, 1, (4097, 1))
+    c = rng.uniform(-1, 1, (65, 2))
+    horner = mpb.Plan(e, gp).eval(xx, c)
+    _lib.lib().mpx_debug_set_eval_1d(2)
+    try:
+        tree_plan = mpb.Plan(e, gp)
+        assert tree_plan.info(_lib.INFO_SMALLK_KERNEL) == 0
+        tree = tree_plan.eval(xx, c)
+    finally:
+        _lib.lib().mpx_debug_set_eval_1d(0)
+    assert rel_err(horner, tree) <= EVAL_RTOL
+    # duplicate exponents: the reference adds both terms; such a list stays on the tree kernel
+    e = np.array([0, 1, 1, 2]).reshape(-1, 1).astype(np.int64)
+    gp = rng.uniform(-1, 1, (4, 1))
+    plan = mpb.Plan(e, gp)
+    assert plan.info(_lib.INFO_SMALLK_KERNEL) != 3
+    c = rng.uniform(-1, 1, (4, 1))
+    xx = rng.uniform(-1, 1, (33, 1))
+    assert rel_err(plan.eval(xx, c), oracle.eval_newton_polynomials(xx, c, e, gp)) <= EVAL_RTOL

@@ -43,7 +43,7 @@ def main():
         torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1))
     ms = float(np.median(ts))
-    kern = {0: "dfma-tree", 1: "tensor-tree", 2: "smem-table"}[plan.info(_lib.INFO_SMALLK_KERNEL)]
+    kern = {0: "dfma-tree", 1: "tensor-tree", 2: "smem-table", 3: "horner-1d"}[plan.info(_lib.INFO_SMALLK_KERNEL)]
     print(f"{tag} N={N} P={P} kernel={kern} {ms:.2f} ms  {P * N / ms / 1e9:.3f}e12 pm/s")
 
 
