@@ -20,6 +20,9 @@ def main():
     ap.add_argument("--workload", default="cfg4")
     ap.add_argument("--k", type=int, default=256)
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--identity", action="store_true",
+                    help="value array = the first k columns of the identity (what array_repr_full transforms): mostly zeros")
+    ap.add_argument("--mode", type=int, default=0, help="test hook: 0 auto, 1 fused slices, 2 one column per lane")
     args = ap.parse_args()
     import torch
     import minterpy_b200 as mpb
@@ -30,8 +33,11 @@ def main():
     plan = mpb.get_plan(e, gp)
     gen = torch.Generator(device="cuda").manual_seed(1)
     vals = torch.rand((N, args.k), generator=gen, dtype=torch.float64, device="cuda") * 2 - 1
+    if args.identity:
+        vals = torch.eye(N, args.k, dtype=torch.float64, device="cuda")
     work = vals.clone()
     lib = _lib.lib()
+    lib.mpx_debug_set_dds_group(args.mode)
     stream = torch.cuda.current_stream().cuda_stream
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > L2 (126 MB)
 
@@ -68,7 +74,7 @@ def main():
     algo = 2.0 * N * args.k * 8
     updates = plan.info(_lib.INFO_DDS_UPDATES) * args.k
     print(json.dumps({"bench": "dds", "workload": args.workload, "N": int(N), "m": int(m),
-                      "k": args.k, "ms": ms, "ms_min": float(min(ts)),
+                      "k": args.k, "values": "identity columns" if args.identity else "uniform(-1, 1)", "ms": ms, "ms_min": float(min(ts)),
                       "coefficients_per_s": N * args.k / (ms * 1e-3),
                       "updates_per_s": updates / (ms * 1e-3),
                       "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9,
