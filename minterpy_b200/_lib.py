@@ -25,6 +25,7 @@ SIGNATURES = {
     "mpx_eval_host": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_int, c_i64, c_vp, c_i64]),
     "mpx_monomials": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_i64, c_int, c_vp]),
     "mpx_dds": (c_int, [c_vp, c_vp, c_int, c_i64, c_vp]),
+    "mpx_dds_ex": (c_int, [c_vp, c_vp, c_int, c_i64, c_int, c_vp]),
     "mpx_dds_host": (c_int, [c_vp, c_vp, c_int, c_i64, c_vp, c_i64]),
     "mpx_apply_dense": (c_int, [c_int, c_vp, c_i64, c_i64, c_i64, c_vp, c_int, c_i64, c_vp,
                                 c_i64, c_vp]),
@@ -51,6 +52,7 @@ DEBUG_SIGNATURES = {
 }
 
 MPX_DENSE_LOWER = 1
+MPX_DDS_MANY_ZEROS = 1
 MPX_OK, MPX_ERR_ARG, MPX_ERR_INCOMPLETE, MPX_ERR_CUDA, MPX_ERR_UNSUPPORTED, MPX_ERR_NOMEM = range(6)
 (INFO_N, INFO_M, INFO_COMPLETE, INFO_EVAL_FMA, INFO_DDS_UPDATES, INFO_LEAVES, INFO_DEVICE,
  INFO_SCRATCH_BYTES, INFO_EVAL_OTHER_FP64, INFO_CHUNKS, INFO_SMALLK_KERNEL,

@@ -87,6 +87,11 @@ extern "C" int mpx_monomials(mpx_plan *pl, const double *xx, int64_t P, int64_t 
 
 extern "C" int mpx_dds(mpx_plan *pl, double *vals, int k, int64_t ld, void *stream)
 {
+    return mpx_dds_ex(pl, vals, k, ld, 0, stream);
+}
+
+extern "C" int mpx_dds_ex(mpx_plan *pl, double *vals, int k, int64_t ld, int flags, void *stream)
+{
     int rc = check_plan(pl);
     if (rc) return rc;
     if (k < 1) return mpx_fail(MPX_ERR_ARG, "k must be >= 1");
@@ -94,7 +99,8 @@ extern "C" int mpx_dds(mpx_plan *pl, double *vals, int k, int64_t ld, void *stre
     if (ld < k) return mpx_fail(MPX_ERR_ARG, "leading dimension too small");
     DeviceGuard dg(pl->device);
     if (!dg.ok) return mpx_fail(MPX_ERR_CUDA, "cannot select the plan's CUDA device");
-    return mpx_launch_dds(pl, vals, k, ld, (cudaStream_t)stream);
+    if (flags & ~MPX_DDS_MANY_ZEROS) return mpx_fail(MPX_ERR_ARG, "unknown dds flag");
+    return mpx_launch_dds(pl, vals, k, ld, (cudaStream_t)stream, flags);
 }
 
 // ---- host-buffer variants ----------------------------------------------------------------

@@ -251,7 +251,7 @@ int mpx_launch_eval(mpx_plan *plan, MpxImage *img, const double *xx, int64_t P, 
                     cudaStream_t stream);
 int mpx_launch_monomials(mpx_plan *plan, const double *xx, int64_t P, int64_t ld_xx,
                          double *out, int64_t ld_out, int triangular, cudaStream_t stream);
-int mpx_launch_dds(mpx_plan *plan, double *vals, int k, int64_t ld, cudaStream_t stream);
+int mpx_launch_dds(mpx_plan *plan, double *vals, int k, int64_t ld, cudaStream_t stream, int flags = 0);
 // make room for `bytes` in the image and order `stream` behind the image's last reader
 int mpx_image_acquire(MpxImage *img, size_t bytes, cudaStream_t stream);
 // record that work reading the image has just been enqueued on `stream`

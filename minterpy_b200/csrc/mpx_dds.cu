@@ -444,7 +444,7 @@ __device__ __noinline__ void dds_redo_columns(double2 *__restrict__ bl, const do
 // the same three instructions return exactly A, and flags them (INC); one integer increment of
 // the bit pattern finishes the division.  tools/div_check.cu compares both forms with __ddiv_rn.
 // `bad` collects what neither form may take: a outside [2^-900, 2^900) other than +0.
-template <bool FLAGGED>
+template <bool FLAGGED, bool ZSAFE = false>
 __device__ __forceinline__ double dds_update_flag(double x, double pv, double d, double y, bool inc,
                                                   bool &bad)
 {
@@ -454,6 +454,17 @@ __device__ __forceinline__ double dds_update_flag(double x, double pv, double d,
     double q2 = __fma_rn(r, y, q);
     const int hi = __double2hiint(a);
     const bool in_range = ((unsigned)(hi & 0x7ff00000) - (123u << 20)) < (1800u << 20);
+    if constexpr (ZSAFE) {
+        // the instantiation for value arrays known to be full of zeros (MPX_DDS_MANY_ZEROS):
+        // +-0 / d is the zero a * y, which has the right sign
+        const bool zero = ((hi & 0x7fffffff) | __double2loint(a)) == 0;
+        bad = bad || !(in_range || zero);
+        if constexpr (FLAGGED) {
+            if (inc && !zero)
+                q2 = __longlong_as_double(__double_as_longlong(q2) + 1);
+        }
+        return zero ? q : q2;
+    }
     const bool plus_zero = (hi | __double2loint(a)) == 0;
     bad = bad || !(in_range || plus_zero);
     if constexpr (FLAGGED) {
@@ -466,7 +477,7 @@ __device__ __forceinline__ double dds_update_flag(double x, double pv, double d,
     return q2;
 }
 
-template <int FW, int H>
+template <int FW, int H, bool ZSAFE>
 __global__ void __launch_bounds__(FW * 32)
 dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_t *__restrict__ woff,
                       const int32_t *__restrict__ wrows, int n_work, const double *__restrict__ dy,
@@ -542,8 +553,8 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
 #pragma unroll
             for (int h = 0; h < H; ++h) {
                 const double2 pv = vp[h * 32];
-                x[h].x = dds_update_flag<true>(x[h].x, pv.x, t0.x, t0.y, inc, bad);
-                x[h].y = dds_update_flag<true>(x[h].y, pv.y, t0.x, t0.y, inc, bad);
+                x[h].x = dds_update_flag<true, ZSAFE>(x[h].x, pv.x, t0.x, t0.y, inc, bad);
+                x[h].y = dds_update_flag<true, ZSAFE>(x[h].y, pv.y, t0.x, t0.y, inc, bad);
             }
             t += L;
             vp += H * 32;
@@ -571,8 +582,8 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
                     const double2 pv = vp[h * 32];
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        x[q][h].x = dds_update_flag<false>(x[q][h].x, pv.x, tq[q].x, tq[q].y, false, bad);
-                        x[q][h].y = dds_update_flag<false>(x[q][h].y, pv.y, tq[q].x, tq[q].y, false, bad);
+                        x[q][h].x = dds_update_flag<false, ZSAFE>(x[q][h].x, pv.x, tq[q].x, tq[q].y, false, bad);
+                        x[q][h].y = dds_update_flag<false, ZSAFE>(x[q][h].y, pv.y, tq[q].x, tq[q].y, false, bad);
                     }
                 }
             } else {
@@ -582,8 +593,8 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const bool inc = (flags >> q) & 1u;
-                        x[q][h].x = dds_update_flag<true>(x[q][h].x, pv.x, tq[q].x, tq[q].y, inc, bad);
-                        x[q][h].y = dds_update_flag<true>(x[q][h].y, pv.y, tq[q].x, tq[q].y, inc, bad);
+                        x[q][h].x = dds_update_flag<true, ZSAFE>(x[q][h].x, pv.x, tq[q].x, tq[q].y, inc, bad);
+                        x[q][h].y = dds_update_flag<true, ZSAFE>(x[q][h].y, pv.y, tq[q].x, tq[q].y, inc, bad);
                     }
                 }
             }
@@ -599,8 +610,8 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
                 const bool inc = (fm[r + j] >> (r + q)) & 1ull;
 #pragma unroll
                 for (int h = 0; h < H; ++h) {
-                    x[q][h].x = dds_update_flag<true>(x[q][h].x, x[j][h].x, tp.x, tp.y, inc, bad);
-                    x[q][h].y = dds_update_flag<true>(x[q][h].y, x[j][h].y, tp.x, tp.y, inc, bad);
+                    x[q][h].x = dds_update_flag<true, ZSAFE>(x[q][h].x, x[j][h].x, tp.x, tp.y, inc, bad);
+                    x[q][h].y = dds_update_flag<true, ZSAFE>(x[q][h].y, x[j][h].y, tp.x, tp.y, inc, bad);
                 }
             }
             t += L;
@@ -739,7 +750,7 @@ dds_fiber_reg_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_t
 // several columns per lane: k, ld and the base address must allow 16-byte accesses, fibers <= 40
 template <int H, int FW = 4>
 static int launch_dds_cols_h(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
-                             bool *handled)
+                             bool *handled, bool zsafe = false)
 {
     int smem_max = 0;
     MPX_CUDA(cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, pl->device));
@@ -752,7 +763,7 @@ static int launch_dds_cols_h(mpx_plan *pl, double *vals, int k, int64_t ld, cuda
         if (dd.n_work == 0) continue;
         if (dd.max_len > 40 || !dd.cols_ok || smem_of(dd) > (size_t)smem_max) return MPX_OK;
     }
-    auto fn = dds_fiber_cols_kernel<FW, H>;
+    auto fn = zsafe ? dds_fiber_cols_kernel<FW, H, true> : dds_fiber_cols_kernel<FW, H, false>;
     MPX_CUDA(mpx_allow_max_smem(fn));
     // (Running all passes over one L2-sized group of columns before the next group was measured:
     // 3 % slower at cfg4 -- the passes are not bound by HBM alone, and smaller launches have
@@ -770,7 +781,7 @@ static int launch_dds_cols_h(mpx_plan *pl, double *vals, int k, int64_t ld, cuda
 }
 
 static int launch_dds_cols(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream,
-                           bool *handled)
+                           bool *handled, bool zsafe)
 {
     *handled = false;
     if ((k & 1) || (ld & 1) || (reinterpret_cast<uintptr_t>(vals) & 15) || k < 34) return MPX_OK;
@@ -786,12 +797,12 @@ static int launch_dds_cols(mpx_plan *pl, double *vals, int k, int64_t ld, cudaSt
     if (fw == 8) return launch_dds_cols_h<2, 8>(pl, vals, k, ld, stream, handled);
     return launch_dds_cols_h<2, 4>(pl, vals, k, ld, stream, handled);
 #else
-    if (k < 128) return launch_dds_cols_h<1>(pl, vals, k, ld, stream, handled);
+    if (k < 128) return launch_dds_cols_h<1>(pl, vals, k, ld, stream, handled, zsafe);
     // two pairs per lane over the multiples of 128 columns, one pair per lane over the rest
     const int k2 = k & ~127;
-    int rc = launch_dds_cols_h<2>(pl, vals, k2, ld, stream, handled);
+    int rc = launch_dds_cols_h<2>(pl, vals, k2, ld, stream, handled, zsafe);
     if (rc != MPX_OK || !*handled || k2 == k) return rc;
-    rc = launch_dds_cols_h<1>(pl, vals + k2, k - k2, ld, stream, handled);
+    rc = launch_dds_cols_h<1>(pl, vals + k2, k - k2, ld, stream, handled, zsafe);
     if (rc == MPX_OK && !*handled)
         return mpx_fail(MPX_ERR_CUDA, "dds: the one-pair kernel refused what the two-pair kernel took");
     return rc;
@@ -916,7 +927,7 @@ static int launch_dds_per_dim(mpx_plan *pl, double *vals, int k, int64_t ld, cud
 static int mpx_test_dds_group = 0;
 extern "C" void mpx_debug_set_dds_group(int on) { mpx_test_dds_group = on; }
 
-int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream)
+int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t stream, int flags)
 {
     if (!pl->complete)
         return mpx_fail(MPX_ERR_INCOMPLETE,
@@ -936,7 +947,7 @@ int mpx_launch_dds(mpx_plan *pl, double *vals, int k, int64_t ld, cudaStream_t s
         bool handled = false;
         int rc = MPX_OK;
         if (!mode) {
-            rc = launch_dds_cols(pl, vals, k, ld, stream, &handled);
+            rc = launch_dds_cols(pl, vals, k, ld, stream, &handled, (flags & MPX_DDS_MANY_ZEROS) != 0);
             if (rc != MPX_OK || handled) return rc;
         }
 #ifdef MPX_TUNING

@@ -177,17 +177,26 @@ class Plan:
         return out.cpu().numpy() if as_numpy else out
 
     # ---- divided differences ----------------------------------------------------------------
-    def dds(self, values):
-        """values (N, k) -> Newton coefficients (N, k); the input is never modified."""
-        if _is_torch(values):
+    def dds(self, values, many_zeros=False, inplace=False):
+        """values (N, k) -> Newton coefficients (N, k); the input is never modified, unless it
+        is a contiguous float64 tensor on the plan's device and ``inplace`` is set.
+        ``many_zeros``: the ``MPX_DDS_MANY_ZEROS`` hint of ``mpx_dds_ex`` (columns of the identity
+        and the like; same bits out, another instantiation of the kernel)."""
+        if _is_torch(values) or many_zeros:
             import torch
             dev = torch.device("cuda", self.device)
-            v = torch.as_tensor(values, dtype=torch.float64, device=dev).clone(
-                memory_format=torch.contiguous_format)
+            as_numpy = not _is_torch(values)
+            if as_numpy:        # a fresh device copy
+                v = torch.as_tensor(np.ascontiguousarray(values, dtype=np.float64), device=dev)
+            else:
+                v = torch.as_tensor(values, dtype=torch.float64, device=dev)
+                if not (inplace and v.is_contiguous() and v.data_ptr() == values.data_ptr()):
+                    v = v.clone(memory_format=torch.contiguous_format)
             stream = torch.cuda.current_stream(dev).cuda_stream
-            rc = _lib.lib().mpx_dds(self._h, v.data_ptr(), v.shape[1], v.stride(0), stream)
+            rc = _lib.lib().mpx_dds_ex(self._h, v.data_ptr(), v.shape[1], v.stride(0),
+                                       _lib.MPX_DDS_MANY_ZEROS if many_zeros else 0, stream)
             _lib.check(rc)
-            return v
+            return v.cpu().numpy() if as_numpy else v
         values = np.ascontiguousarray(values, dtype=np.float64)
         out = _host_result(values.shape)      # page-locked for large results: faster download
         k = values.shape[1]

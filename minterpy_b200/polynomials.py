@@ -314,14 +314,19 @@ class DDSOperator(_Operator):
 
     def _get_array_repr(self):
         """The N x N matrix (dds of the identity, like ``build_l2n_matrix_dds``)."""
-        return api.dds(np.eye(len(self.grid.multi_index)), self.grid.tree)
+        plan = get_plan(np.asarray(self.grid.multi_index.exponents),
+                        np.asarray(self.grid.generating_points))
+        return plan.dds(np.eye(len(self.grid.multi_index)), many_zeros=True)
 
     def full_on_device(self, device=None):
-        """The same matrix as a CUDA tensor: identity built and transformed on the device."""
+        """The same matrix as a CUDA tensor: identity built and transformed on the device, in
+        place, with the kernel instantiation for arrays full of zeros (``MPX_DDS_MANY_ZEROS``)."""
         import torch
-        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
-        return api.dds(torch.eye(len(self.grid.multi_index), dtype=torch.float64, device=dev),
-                       self.grid.tree)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        plan = get_plan(np.asarray(self.grid.multi_index.exponents),
+                        np.asarray(self.grid.generating_points), device=dev.index)
+        eye = torch.eye(len(self.grid.multi_index), dtype=torch.float64, device=dev)
+        return plan.dds(eye, many_zeros=True, inplace=True)
 
 
 class NodeEvalOperator(_Operator):

@@ -26,7 +26,7 @@ class OraclePlan:
     def monomials(self, xx, triangular=False):
         return oracle.eval_newton_monomials(xx, self.e, self.gp, triangular)
 
-    def dds(self, values):
+    def dds(self, values, many_zeros=False, inplace=False):
         return oracle.dds(values, self.e, self.gp)
 
 

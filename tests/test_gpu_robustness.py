@@ -311,7 +311,13 @@ def test_dds_kernels_agree_bit_for_bit_on_ragged_widths_and_special_values(mpb, 
         for k in (32, 64, 256):
             eye = np.eye(N, k, k=-int(rng.integers(0, max(1, N - k))))
             got = plan.dds(torch.as_tensor(eye, device="cuda")).cpu().numpy()
-            assert _same_bits(got, oracle.dds(eye, e, gp)), (tag, "identity", k)
+            ref = oracle.dds(eye, e, gp)
+            assert _same_bits(got, ref), (tag, "identity", k)
+            # the MPX_DDS_MANY_ZEROS instantiation (mpx_dds_ex): the same bits, on zeros and on
+            # ordinary and special values alike
+            assert _same_bits(plan.dds(eye, many_zeros=True), ref), (tag, "identity, hint", k)
+            hinted = plan.dds(v, many_zeros=True, inplace=False).cpu().numpy()
+            assert hinted.shape == want.shape and _same_bits_up_to_nan_payload(hinted, want), (tag, "hint", k)
 
 
 def test_uniform_control_tree_kernel_is_bit_identical_to_the_ring_kernel(mpb, golden_cfg, golden_small):

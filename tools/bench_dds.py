@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--identity", action="store_true",
                     help="value array = the first k columns of the identity (what array_repr_full transforms): mostly zeros")
+    ap.add_argument("--hint", action="store_true", help="pass MPX_DDS_MANY_ZEROS (mpx_dds_ex)")
     ap.add_argument("--mode", type=int, default=0, help="test hook: 0 auto, 1 fused slices, 2 one column per lane")
     args = ap.parse_args()
     import torch
@@ -46,7 +47,8 @@ def main():
         flush.zero_()                   # evict the value array from L2 between iterations
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        _lib.check(lib.mpx_dds(plan._h, work.data_ptr(), args.k, work.stride(0), stream))
+        _lib.check(lib.mpx_dds_ex(plan._h, work.data_ptr(), args.k, work.stride(0),
+                                  _lib.MPX_DDS_MANY_ZEROS if args.hint else 0, stream))
         e1.record()
         torch.cuda.synchronize()
         return e0.elapsed_time(e1)
@@ -74,7 +76,7 @@ def main():
     algo = 2.0 * N * args.k * 8
     updates = plan.info(_lib.INFO_DDS_UPDATES) * args.k
     print(json.dumps({"bench": "dds", "workload": args.workload, "N": int(N), "m": int(m),
-                      "k": args.k, "values": "identity columns" if args.identity else "uniform(-1, 1)", "ms": ms, "ms_min": float(min(ts)),
+                      "k": args.k, "values": "identity columns" if args.identity else "uniform(-1, 1)", "many_zeros_hint": bool(args.hint), "ms": ms, "ms_min": float(min(ts)),
                       "coefficients_per_s": N * args.k / (ms * 1e-3),
                       "updates_per_s": updates / (ms * 1e-3),
                       "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9,
