@@ -159,7 +159,7 @@ int mpx_dds(mpx_plan *plan, double *vals, int k, int64_t ld, void *stream);
  * (array_repr_full, src/minterpy/core/ABC/operator_abstract.py:47-80 over
  * transformations/utils.py:155-179).  Zeros put -0 numerators into every step, which the
  * default instantiation hands to its true-division redo path; with the hint a second
- * instantiation keeps them on the fast path (cfg4, 256 identity columns: 1.33 -> 0.32 ms) at a
+ * instantiation keeps them on the fast path (cfg4, 256 identity columns: 0.62 -> 0.32 ms) at a
  * cost of 8 % on ordinary values.  Results are bit-identical with and without the hint.
  */
 #define MPX_DDS_MANY_ZEROS 1

@@ -410,11 +410,31 @@ dds_fiber_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_t *__
 // "not valid" into one sticky flag per lane; a flagged lane redoes its columns with true
 // divisions from the values still unchanged in global memory (dds_redo_columns).
 // Buffer layout: row r, pair h of the lane at double2 index (r * H + h) * 32 + lane.
+// One update of the redo path: the fast division where it is exact (numerator in range, or a
+// zero of either sign), the true division by the true divisor otherwise.
+__device__ __forceinline__ double dds_redo_one(double x, double pv, double2 t, bool inc,
+                                               const double *__restrict__ gcol, int r, int i)
+{
+    const double a = __dsub_rn(x, pv);
+    const double q = __dmul_rn(a, t.y);
+    const double rem = __fma_rn(-t.x, q, a);
+    double q2 = __fma_rn(rem, t.y, q);
+    const int hi = __double2hiint(a);
+    if (((unsigned)(hi & 0x7ff00000) - (123u << 20)) < (1800u << 20)) {
+        if (inc) q2 = __longlong_as_double(__double_as_longlong(q2) + 1);
+        return q2;
+    }
+    if (((hi & 0x7fffffff) | __double2loint(a)) == 0) return q;    // +-0 / d: the zero a * y
+    return dds_true_division(a, __dsub_rn(gcol[r], gcol[i - 1]));  // the subtraction the host tabulated
+}
+
 template <int H>
 __device__ __noinline__ void dds_redo_columns(double2 *__restrict__ bl, const double *__restrict__ vals,
                                               int64_t ld, int64_t col0, unsigned active,
                                               const int32_t *__restrict__ rows, int len,
-                                              const double *__restrict__ gcol)
+                                              const double *__restrict__ gcol,
+                                              const double2 *__restrict__ dy2,
+                                              const unsigned long long *__restrict__ fm, int L)
 {
     for (int r = 0; r < len; ++r)
 #pragma unroll
@@ -423,13 +443,14 @@ __device__ __noinline__ void dds_redo_columns(double2 *__restrict__ bl, const do
                 bl[(r * H + h) * 32] = *reinterpret_cast<const double2 *>(vals + (int64_t)rows[r] * ld + col0 + 64 * h);
     for (int i = 1; i < len; ++i)
         for (int r = i; r < len; ++r) {
-            const double d = __dsub_rn(gcol[r], gcol[i - 1]);   // the subtraction the host tabulated
+            const double2 t = dy2[(i - 1) * L + r];
+            const bool inc = (fm[i - 1] >> r) & 1ull;
 #pragma unroll
             for (int h = 0; h < H; ++h) {
                 double2 x = bl[(r * H + h) * 32];
                 const double2 pv = bl[((i - 1) * H + h) * 32];
-                x.x = __ddiv_rn(__dsub_rn(x.x, pv.x), d);
-                x.y = __ddiv_rn(__dsub_rn(x.y, pv.y), d);
+                x.x = dds_redo_one(x.x, pv.x, t, inc, gcol, r, i);
+                x.y = dds_redo_one(x.y, pv.y, t, inc, gcol, r, i);
                 bl[(r * H + h) * 32] = x;
             }
         }
@@ -625,7 +646,7 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     // (a lane beyond column k swept zeros, which produce -0: its flag means nothing.  Lanes with
     // only one of two pairs inside do not occur: the launcher gives the columns behind the last
     // multiple of 128 to the one-pair instantiation.)
-    if (bad && active) dds_redo_columns<H>(bl, vals, ld, col0, active, rows, len, gcol);
+    if (bad && active) dds_redo_columns<H>(bl, vals, ld, col0, active, rows, len, gcol, dy2, fm, L);
 #endif
     // Write back rows 1..len-1 (element 0 of a fiber never changes), again one bulk copy per row
     fence_proxy_async_smem();

@@ -56,7 +56,9 @@ double reciprocal_or_zero(double dv)
     std::memcpy(&bits, &dv, 8);
     const int ex = (int)((bits >> 52) & 0x7ff);
     const uint64_t mant = bits & 0xfffffffffffffull;
-    const bool ordinary = ex >= 1023 - 200 && ex <= 1023 + 200 && mant != 0xfffffffffffffull;
+    // |d| in [2^-100, 2^100]: with numerators in [2^-900, 2^900) neither the quotient nor the
+    // remainder a - d q can leave the normal range (a wider allowance could overflow a * y)
+    const bool ordinary = ex >= 1023 - 100 && ex <= 1023 + 100 && mant != 0xfffffffffffffull;
     return ordinary ? 1.0 / dv : 0.0;      // host division: RN(1/d)
 }
 
@@ -67,7 +69,7 @@ bool all_ones_divisor(double dv, double *pw)
     std::memcpy(&bits, &dv, 8);
     const int ex = (int)((bits >> 52) & 0x7ff);
     const uint64_t mant = bits & 0xfffffffffffffull;
-    if (mant != 0xfffffffffffffull || ex < 1023 - 200 || ex > 1023 + 200) return false;
+    if (mant != 0xfffffffffffffull || ex < 1023 - 100 || ex > 1023 + 100) return false;
     *pw = std::ldexp(dv < 0 ? -1.0 : 1.0, ex - 1023 + 1);
     return true;
 }
