@@ -99,6 +99,8 @@ struct DdsDim {
     int n_work = 0;
     int32_t *d_woff = nullptr;  // n_work + 1
     int32_t *d_wrows = nullptr; // rows of those fibers
+    int32_t *d_wpad = nullptr;  // the same rows, max_len slots per fiber (column kernel: the row
+                                // numbers can be read before the fiber's length is known)
     double *d_dy = nullptr;     // (L x L) pairs (divisor, reciprocal or 0), 2 doubles each
     double *d_gcol = nullptr;   // (L) generating points of this dimension
     // several-columns-per-lane kernel (max_len <= 40): (divisor, reciprocal) pairs as d_dy, except

@@ -518,9 +518,12 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     unsigned active = 0;
 #pragma unroll
     for (int h = 0; h < H; ++h) active |= (col0 + 64 * h < k) ? 1u << h : 0u;
-    const int o = valid ? woff[f] : 0;
-    const int len = valid ? woff[f + 1] - o : 0;
-    const int32_t *rows = wrows + o;
+    // `wrows` holds L row numbers per fiber (padded): the lane's rows for the gather (row `lane`)
+    // and for the write-back (row `lane + 1`) are read while the fiber's length is on its way
+    const int32_t *rows = wrows + (size_t)(valid ? f : 0) * L;
+    const int32_t row_in = rows[lane < L ? lane : L - 1];
+    const int32_t row_out = rows[lane + 1 < L ? lane + 1 : L - 1];
+    const int len = valid ? woff[f + 1] - woff[f] : 0;
     double2 *bw = dy2 + L * L + (size_t)warp * L * H * 32;               // this warp's fiber buffer
     double2 *bl = bw + lane;                                             // this lane's slots
     // Gather: row r of the fiber is ONE contiguous piece of global memory (the warp's 64 H value
@@ -543,7 +546,9 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     __syncwarp();
     if (valid) {
         if (lane == 0) mbar_arrive_expect_tx(bar, row_bytes * (uint32_t)len);
-        for (int r = lane; r < len; r += 32)
+        if (lane < len)
+            bulk_g2s(bw + (size_t)lane * H * 32, vals + (int64_t)row_in * ld + cw0, row_bytes, bar);
+        for (int r = lane + 32; r < len; r += 32)
             bulk_g2s(bw + (size_t)r * H * 32, vals + (int64_t)rows[r] * ld + cw0, row_bytes, bar);
     }
     // the tables are staged while the rows are on their way
@@ -651,7 +656,9 @@ dds_fiber_cols_kernel(double *__restrict__ vals, int64_t ld, int k, const int32_
     // Write back rows 1..len-1 (element 0 of a fiber never changes), again one bulk copy per row
     fence_proxy_async_smem();
     __syncwarp();
-    for (int rr = 1 + lane; rr < len; rr += 32)
+    if (1 + lane < len)
+        bulk_s2g(vals + (int64_t)row_out * ld + cw0, bw + (size_t)(1 + lane) * H * 32, row_bytes);
+    for (int rr = 33 + lane; rr < len; rr += 32)
         bulk_s2g(vals + (int64_t)rows[rr] * ld + cw0, bw + (size_t)rr * H * 32, row_bytes);
     bulk_commit_and_wait_read();          // the buffer must outlive the copies that read it
 }
@@ -793,7 +800,7 @@ static int launch_dds_cols_h(mpx_plan *pl, double *vals, int k, int64_t ld, cuda
         const DdsDim &dd = pl->dds[d];
         if (dd.n_work == 0) continue;
         dim3 grid((unsigned)((dd.n_work + FW - 1) / FW), (unsigned)((k + 64 * H - 1) / (64 * H)), 1);
-        fn<<<grid, FW * 32, smem_of(dd), stream>>>(vals, ld, k, dd.d_woff, dd.d_wrows, dd.n_work,
+        fn<<<grid, FW * 32, smem_of(dd), stream>>>(vals, ld, k, dd.d_woff, dd.d_wpad, dd.n_work,
                                                    dd.d_dy2, dd.d_fmask, dd.d_gcol, dd.max_len);
         MPX_CUDA(cudaGetLastError());
     }

@@ -714,6 +714,14 @@ extern "C" int mpx_plan_create(int device, const int64_t *exponents_h, int64_t N
                     if (dd.cols_ok) {
                         if ((rc = upload(&dd.d_dy2, dy2v)) != MPX_OK) return rc;
                         if ((rc = upload(&dd.d_fmask, fmask)) != MPX_OK) return rc;
+                        // rows at a fixed stride (slots behind a fiber's end repeat its last row)
+                        std::vector<int32_t> wpad((size_t)dd.n_work * max_len + 64, 0);
+                        for (int f = 0; f < dd.n_work; ++f) {
+                            const int len = woff[f + 1] - woff[f];
+                            for (int r = 0; r < max_len; ++r)
+                                wpad[(size_t)f * max_len + r] = wrows[woff[f] + (r < len ? r : len - 1)];
+                        }
+                        if ((rc = upload(&dd.d_wpad, wpad)) != MPX_OK) return rc;
                     }
                 }
                 if (max_len <= MPX_DDS_REG_LEN) {
@@ -788,6 +796,7 @@ extern "C" void mpx_plan_destroy(mpx_plan *pl)
         cudaFree(dd.d_diff);
         cudaFree(dd.d_woff);
         cudaFree(dd.d_wrows);
+        cudaFree(dd.d_wpad);
         cudaFree(dd.d_dy);
         cudaFree(dd.d_dy2);
         cudaFree(dd.d_fmask);
